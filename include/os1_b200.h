@@ -1,0 +1,118 @@
+/* os1_b200.h — C ABI of the B200-native ORB front end and Hamming consumer for os1 (ORB-SLAM2 monocular).
+ *
+ * Plain pointers and sizes only; no C++ or torch types cross this boundary and no exception escapes it.
+ * Every function returns 0 on success or a negative OS1_E_* code; os1_last_error() gives the text.
+ * Citations are into the reference tree (AlejandroSilvestri/os1).  The header-only C++ adapter
+ * include/ORBextractor.h keeps the reference's ORB_SLAM2::ORBextractor class on top of these calls;
+ * INTEGRATION.md shows the binding a maintainer adds to the reference.
+ *
+ * Threading: a handle owns one CUDA stream and its device buffers; calls on one handle must be serialised
+ * by the caller (the reference calls its extractor from the tracker thread only, src/System.cc:64-66, and
+ * the object is not re-entrant, src/ORBextractor.cc:979-986).  Distinct handles are independent and may
+ * live on different GPUs.  There is no CPU fallback: without a CUDA device every call fails with OS1_E_CUDA.
+ */
+#ifndef OS1_B200_H
+#define OS1_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OS1_OK 0
+#define OS1_E_INVALID (-1)     /* bad argument */
+#define OS1_E_CUDA (-2)        /* CUDA runtime / driver failure (text in os1_last_error) */
+#define OS1_E_CAPACITY (-3)    /* a caller-supplied or internal capacity was exceeded */
+#define OS1_E_UNSUPPORTED (-4) /* configuration outside the supported range (see DESIGN.md "limits") */
+
+typedef struct os1_orb os1_orb;
+
+/* Binary layout of cv::KeyPoint (28 bytes): what the reference stores in Frame::mvKeys. */
+typedef struct os1_keypoint {
+    float x, y;        /* pt, in level-0 pixel units (src/ORBextractor.cc:959-965) */
+    float size;        /* (float)(int)(31 * mvScaleFactor[octave])  (:877,:888) */
+    float angle;       /* degrees [0,360), cv::fastAtan2 of the intensity centroid (:86-113) */
+    float response;    /* FAST score (cv::FAST response) */
+    int32_t octave;    /* pyramid level (:887) */
+    int32_t class_id;  /* always -1 */
+} os1_keypoint;
+
+/* ---- extractor: replaces ORB_SLAM2::ORBextractor (include/ORBextractor.h:150-321) ------------------- */
+
+/* ORBextractor::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)  src/ORBextractor.cc:442-502.
+ * `device` is the CUDA ordinal the handle lives on. */
+int os1_orb_create(os1_orb** out, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device);
+/* ~ORBextractor (include/ORBextractor.h:170).  Frees every device and pinned buffer of the handle. */
+int os1_orb_destroy(os1_orb* h);
+/* Text of the last failure on this handle (h == NULL: last failure of a call that had no handle). */
+const char* os1_last_error(const os1_orb* h);
+
+/* GetLevels / GetScaleFactor  include/ORBextractor.h:194-203 */
+int os1_orb_get_levels(const os1_orb* h);
+float os1_orb_get_scale_factor(const os1_orb* h);
+/* GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares / GetInverseScaleSigmaSquares
+ * include/ORBextractor.h:210-239 — each array receives nlevels floats (NULL pointers are skipped). */
+int os1_orb_get_tables(const os1_orb* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2);
+/* mnFeaturesPerLevel (src/ORBextractor.cc:467-478): nlevels ints. */
+int os1_orb_get_features_per_level(const os1_orb* h, int* quota);
+/* Upper bound of keypoints one frame can return (nfeatures plus the quadtree's overshoot). */
+int os1_orb_max_keypoints(const os1_orb* h);
+
+/* Pre-size the device buffers for `max_frames` frames of rows x cols (otherwise done lazily by the first
+ * extract call; a steady-state call allocates nothing). */
+int os1_orb_reserve(os1_orb* h, int rows, int cols, int max_frames);
+
+/* ORBextractor::operator()(image, mask, keypoints, descriptors)   src/ORBextractor.cc:907-969  (mask ignored,
+ * include/ORBextractor.h:184).  HOST buffers; synchronous.  image: rows x cols CV_8UC1 with `step` bytes per
+ * row.  kp: kp_cap records; desc: kp_cap x 32 bytes (row i <-> keypoint i); *n receives the count.
+ * Empty image (rows or cols == 0, or image == NULL) returns OS1_OK and leaves the outputs untouched (:910-911). */
+int os1_orb_extract(os1_orb* h, const uint8_t* image, int rows, int cols, size_t step, os1_keypoint* kp, int kp_cap,
+                    uint8_t* desc, int* n);
+
+/* The same on a batch of equally sized frames (frame f starts at frames + f*frame_stride).
+ * frames_on_device / out_on_device say whether those pointers are device memory of the handle's GPU.
+ * Outputs are slabs of cap_per_frame records per frame: kp[f*cap + i], desc[(f*cap + i)*32], counts[f].
+ * With every buffer on the device the call only enqueues work on the handle's stream (see os1_orb_synchronize);
+ * device-side failures are then reported by os1_orb_synchronize. */
+int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int rows, int cols, size_t step, size_t frame_stride,
+                          int frames_on_device, os1_keypoint* kp, uint8_t* desc, int cap_per_frame, int* counts, int out_on_device);
+int os1_orb_synchronize(os1_orb* h);
+/* Make the handle enqueue on a caller-owned cudaStream_t (NULL restores the handle's own stream). */
+int os1_orb_set_stream(os1_orb* h, void* cuda_stream);
+/* Number of kernels one extract call launches (for launch accounting). */
+int os1_orb_launches_per_call(const os1_orb* h);
+
+/* ---- stage accessors (parity tests; frame index refers to the last extract call) --------------------- */
+/* public mvImagePyramid (include/ORBextractor.h:245), without the never-read 19-px border: w*h bytes, packed. */
+int os1_orb_level_size(const os1_orb* h, int level, int* w, int* hh);
+int os1_orb_get_pyramid_level(os1_orb* h, int frame, int level, uint8_t* out_host);
+/* vToDistributeKeys of ComputeKeyPointsOctTree (src/ORBextractor.cc:816-870): n x {x, y, response}, coordinates
+ * relative to (minBorderX, minBorderY), in the reference's order. */
+int os1_orb_get_candidates(os1_orb* h, int frame, int level, int32_t* xys, int cap, int* n);
+/* allKeypoints[level] after DistributeOctTree (:873-889): n x {x, y, response} in level pixels, list order. */
+int os1_orb_get_level_keypoints(os1_orb* h, int frame, int level, int32_t* xys, int cap, int* n);
+
+/* ---- Hamming consumer: replaces ORBmatcher::DescriptorDistance inside the matchers' scan loops ------------ */
+/* static int ORBmatcher::DescriptorDistance(a, b)   src/ORBmatcher.cc:1605-1621 — scalar, host. */
+int os1_descriptor_distance(const uint8_t* a, const uint8_t* b);
+
+/* All-pairs best / second best (the scan of src/ORBmatcher.cc:431-452 with the whole of B as candidate list,
+ * ascending index order, no claim bookkeeping): for every row i of A (nA x 32 bytes)
+ *   best_idx[i] = first index of the minimum distance, best_dist[i] = that distance,
+ *   second_dist[i] = second smallest distance VALUE (== best when the minimum occurs twice);
+ * -1 / INT_MAX / INT_MAX when nB == 0.  on_device: all five pointers are device memory of `device`;
+ * otherwise they are host memory and the call is synchronous.  cuda_stream may be NULL. */
+int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist,
+                     int on_device, int device, void* cuda_stream);
+/* Windowed variant: row i is compared with B[cand[ptr[i] .. ptr[i+1])] in list order — the candidate lists
+ * Frame::GetFeaturesInArea returns (src/Frame.cc:209-262) as used at src/ORBmatcher.cc:420, :1349, :73.
+ * ptr has nA+1 entries.  best_idx is an index into B. */
+int os1_hamming_window(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, int32_t* best_idx,
+                       int32_t* best_dist, int32_t* second_dist, int on_device, int device, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OS1_B200_H */

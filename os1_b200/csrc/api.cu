@@ -1,0 +1,690 @@
+// C ABI of os1_b200 (include/os1_b200.h): handle management, geometry/tables that the reference computes in
+// its constructor and at the top of each stage, buffer ownership, and the four-kernel extraction pipeline.
+#include "../../include/os1_b200.h"
+#include "os1_internal.cuh"
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string t_err;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= bytes) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+
+} // namespace
+
+struct os1_orb {
+    // constructor state (ORBextractor.cc:442-502)
+    int nfeatures, nlevels, iniTh, minTh;
+    double scaleFactor;      // ORBextractor.h:313: a double that holds (double)(float)argument
+    std::vector<float> scale, inv, sigma2, invsigma2;
+    std::vector<int> quota;
+    int maxQuota;
+
+    int device;
+    cudaStream_t ownStream = nullptr, stream = nullptr;
+    std::string err;
+
+    // geometry of the current resolution
+    bool haveGeom = false;
+    Geometry geom;
+    int maxCells = 0;
+    int batchCap = 0;
+    PyramidPlan* plan = nullptr;
+    DevBuf rtab, ptab, slab, cellCnt, stage, cand, code, node, candCount, lvKp, lvCount, status, outKp, outDesc, outCount;
+    int lastFrames = 0;
+    const uint8_t* lastLvl0 = nullptr; long long lastLvl0Stride = 0; int lastLvl0Pitch = 0;
+    // pinned host mirrors for the host-buffer path
+    void* hostOut = nullptr; size_t hostOutBytes = 0;
+    int* hostStatus = nullptr;
+};
+
+namespace {
+
+int fail(os1_orb* h, int code, const std::string& msg)
+{
+    if (h) h->err = msg;
+    t_err = msg;
+    return code;
+}
+int cuda_fail(os1_orb* h, cudaError_t e, const char* what)
+{
+    cudaGetLastError();
+    return fail(h, OS1_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(call, what)                                          \
+    do {                                                        \
+        cudaError_t _e = (call);                                \
+        if (_e != cudaSuccess) return cuda_fail(h, _e, what);   \
+    } while (0)
+
+inline int cv_round(float v) { return (int)lrintf(v); }
+inline int cv_floor(float v) { int i = (int)v; return i - (i > v); }
+
+// scale tables and per-level quotas exactly as the reference constructor computes them (:447-478)
+void build_tables(os1_orb* h)
+{
+    const int L = h->nlevels;
+    h->scale.assign(L, 0); h->sigma2.assign(L, 0); h->inv.assign(L, 0); h->invsigma2.assign(L, 0); h->quota.assign(L, 0);
+    h->scale[0] = 1.0f; h->sigma2[0] = 1.0f;
+    for (int i = 1; i < L; i++) {
+        h->scale[i] = (float)(h->scale[i - 1] * h->scaleFactor);
+        h->sigma2[i] = h->scale[i] * h->scale[i];
+    }
+    for (int i = 0; i < L; i++) { h->inv[i] = 1.0f / h->scale[i]; h->invsigma2[i] = 1.0f / h->sigma2[i]; }
+    float factor = (float)(1.0f / h->scaleFactor);
+    float per = h->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)L));
+    int sum = 0;
+    for (int l = 0; l < L - 1; l++) {
+        h->quota[l] = cv_round(per);
+        sum += h->quota[l];
+        per *= factor;
+    }
+    h->quota[L - 1] = std::max(h->nfeatures - sum, 0);
+    h->maxQuota = 0;
+    for (int l = 0; l < L; l++) h->maxQuota = std::max(h->maxQuota, h->quota[l]);
+}
+
+short sat_short(float v)
+{
+    int i = cv_round(v);
+    return (short)(i < -32768 ? -32768 : i > 32767 ? 32767 : i);
+}
+
+} // namespace
+
+// cv::resize INTER_LINEAR taps of one axis: first/second source index (already clamped
+// the way cv::resize clamps them on that axis) and the two 11-bit coefficients.
+void os1_host_resize_taps(int ssize, int dsize, bool vertical, std::vector<short>& s0, std::vector<short>& s1, std::vector<short>& c0,
+                          std::vector<short>& c1)
+{
+    const double inv_scale = (double)dsize / ssize;
+    const double scale = 1. / inv_scale;
+    s0.resize(dsize); s1.resize(dsize); c0.resize(dsize); c1.resize(dsize);
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = cv_floor(f);
+        f -= s;
+        if (!vertical) {
+            // horizontal: out-of-range taps reset the weight (xofs / alpha tables)
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= ssize - 1) { f = 0; s = ssize - 1; }
+            s0[d] = (short)s; s1[d] = (short)std::min(s + 1, ssize - 1);
+        } else {
+            // vertical: the weight is kept and the two ROW INDICES are clamped
+            s0[d] = (short)std::min(std::max(s, 0), ssize - 1);
+            s1[d] = (short)std::min(std::max(s + 1, 0), ssize - 1);
+        }
+        c0[d] = sat_short((1.f - f) * 2048.f);
+        c1[d] = sat_short(f * 2048.f);
+    }
+}
+
+namespace {
+
+// DivideNode's split bits along one axis for every coordinate (ORBextractor.cc:515-516, :547-557), spread to
+// every second bit: depth d (1-based) sits at bit 2*(PATH_BITS-d) (+1 for y).  For x the root index
+// (:584-601) goes above the path bits.
+void build_path_table(int extent, int nIni, bool isX, std::vector<uint32_t>& out)
+{
+    const int D = OS1_PATH_BITS;
+    out.resize(extent);
+    const float hX = (float)extent / nIni;
+    for (int p = 0; p < extent; p++) {
+        int a = 0, b = extent;
+        uint32_t code = 0;
+        if (isX) {
+            int r = (int)((float)p / hX);
+            if (r >= nIni) r = nIni - 1;
+            a = (int)(hX * (float)r);
+            b = (int)(hX * (float)(r + 1));
+            code = (uint32_t)r << (2 * D);
+        }
+        for (int d = 1; d <= D; d++) {
+            const int half = (int)ceil((float)(b - a) / 2);
+            const int mid = a + half;
+            const int bit = ((float)p < (float)mid) ? 0 : 1;
+            if (bit) a = mid; else b = mid;
+            code |= (uint32_t)bit << (2 * (D - d) + (isX ? 0 : 1));
+        }
+        out[p] = code;
+    }
+}
+
+int build_geometry(os1_orb* h, int rows, int cols)
+{
+    Geometry& g = h->geom;
+    memset(&g, 0, sizeof(g));
+    const int L = h->nlevels;
+    g.nlevels = L; g.rows = rows; g.cols = cols; g.iniTh = h->iniTh; g.minTh = h->minTh;
+    long long slab = 0, candOff = 0;
+    int cellOff = 0, groupOff = 0, kpOff = 0;
+    std::vector<short4> rtab;
+    std::vector<uint32_t> ptab;
+    h->maxCells = 0;
+    for (int l = 0; l < L; l++) {
+        LevelGeom& v = g.lv[l];
+        v.w = cv_round((float)cols * h->inv[l]);                          // :976
+        v.h = cv_round((float)rows * h->inv[l]);
+        if (v.w > 4096 + 32 || v.h > 4096 + 32) return fail(h, OS1_E_UNSUPPORTED, "image side above 4128 px");
+        v.pitch = (v.w + 63) & ~63;
+        v.off = slab;
+        slab += (long long)v.pitch * v.h;
+        slab = (slab + 255) & ~255LL;
+        v.maxBX = v.w - OS1_EDGE + 3; v.maxBY = v.h - OS1_EDGE + 3;     // :809-810
+        v.W = v.maxBX - OS1_BORDER; v.H = v.maxBY - OS1_BORDER;
+        const float width = (float)v.W, height = (float)v.H;
+        v.nCols = (int)(width / 30.f); v.nRows = (int)(height / 30.f);   // :820-821
+        if (v.nCols < 1 || v.nRows < 1)
+            return fail(h, OS1_E_UNSUPPORTED, "image too small for this many pyramid levels (a level is below 62 px; the reference divides by zero there)");
+        v.wCell = (int)ceil(width / v.nCols); v.hCell = (int)ceil(height / v.nRows);   // :822-823
+        v.nCells = v.nCols * v.nRows;
+        v.cellOff = cellOff; cellOff += v.nCells;
+        v.cellCap = ((v.wCell + 1) / 2) * ((v.hCell + 1) / 2);
+        v.candCap = v.nCells * v.cellCap;
+        if (v.candCap >= (1 << 24)) return fail(h, OS1_E_UNSUPPORTED, "more than 2^24 candidate slots in one level");
+        v.candOff = candOff; candOff += v.candCap;
+        v.groupsPerRow = (v.nCols + FAST_G - 1) / FAST_G;
+        v.groupOff = groupOff; groupOff += v.groupsPerRow * v.nRows;
+        h->maxCells = std::max(h->maxCells, v.nCells);
+        v.nIni = (int)roundf((float)v.W / v.H);                            // :575
+        if (v.nIni < 1) return fail(h, OS1_E_UNSUPPORTED, "portrait images taller than 2:1 (the reference's nIni is 0 there)");
+        v.quota = h->quota[l];
+        v.xsOff = (int)ptab.size();
+        { std::vector<uint32_t> t; build_path_table(v.W, v.nIni, true, t); ptab.insert(ptab.end(), t.begin(), t.end()); }
+        v.ysOff = (int)ptab.size();
+        { std::vector<uint32_t> t; build_path_table(v.H, 1, false, t); ptab.insert(ptab.end(), t.begin(), t.end()); }
+        v.kpCap = std::max(v.quota + 2, 4 * v.nIni) + 2;
+        v.kpOff = kpOff; kpOff += v.kpCap;
+        v.scale = h->scale[l];
+        v.kpSize = (float)(int)(31 * h->scale[l]);                         // :877
+        if (l > 0) {
+            std::vector<short> s0, s1, c0, c1;
+            v.rxOff = (int)rtab.size();
+            os1_host_resize_taps(g.lv[l - 1].w, v.w, false, s0, s1, c0, c1);
+            for (int i = 0; i < v.w; i++) rtab.push_back(make_short4(s0[i], s1[i], c0[i], c1[i]));
+            v.ryOff = (int)rtab.size();
+            os1_host_resize_taps(g.lv[l - 1].h, v.h, true, s0, s1, c0, c1);
+            for (int i = 0; i < v.h; i++) rtab.push_back(make_short4(s0[i], s1[i], c0[i], c1[i]));
+            if (g.lv[l - 1].w == 2 * v.w && g.lv[l - 1].h == 2 * v.h)
+                return fail(h, OS1_E_UNSUPPORTED, "scaleFactor 2.0: cv::resize silently switches to INTER_AREA there (not implemented)");
+        }
+    }
+    g.slabBytes = slab;
+    g.cellsPerFrame = cellOff;
+    g.groupsPerFrame = groupOff;
+    g.kpCapPerFrame = kpOff;
+    g.candPerFrame = candOff;
+    if (rtab.empty()) rtab.push_back(make_short4(0, 0, 0, 0));
+    CK(h->rtab.ensure(rtab.size() * sizeof(short4)), "cudaMalloc(rtab)");
+    CK(h->ptab.ensure(ptab.size() * sizeof(uint32_t)), "cudaMalloc(ptab)");
+    CK(cudaMemcpy(h->rtab.p, rtab.data(), rtab.size() * sizeof(short4), cudaMemcpyHostToDevice), "upload resize tables");
+    CK(cudaMemcpy(h->ptab.p, ptab.data(), ptab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice), "upload path tables");
+    if (h->plan) os1_pyramid_plan_destroy(h->plan);
+    // coarsest-level tile: small for single frames (more CTAs), the plan is per resolution
+    h->plan = os1_pyramid_plan_create(g, 32, 16);
+    h->haveGeom = true;
+    h->batchCap = 0;
+    return OS1_OK;
+}
+
+int ensure(os1_orb* h, int rows, int cols, int nframes)
+{
+    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    if (!h->haveGeom || h->geom.rows != rows || h->geom.cols != cols) {
+        if (h->haveGeom) CK(cudaStreamSynchronize(h->stream), "sync before re-planning");
+        int rc = build_geometry(h, rows, cols);
+        if (rc) return rc;
+    }
+    if (nframes > h->batchCap) {
+        const Geometry& g = h->geom;
+        CK(cudaStreamSynchronize(h->stream), "sync before growing buffers");
+        const size_t B = (size_t)nframes;
+        CK(h->slab.ensure(B * g.slabBytes + 256), "cudaMalloc(pyramid slab)");
+        CK(h->cellCnt.ensure(B * g.cellsPerFrame * 4), "cudaMalloc(cell counts)");
+        CK(h->stage.ensure(B * g.candPerFrame * 4), "cudaMalloc(candidate staging)");
+        CK(h->cand.ensure(B * g.candPerFrame * 4), "cudaMalloc(candidates)");
+        CK(h->code.ensure(B * g.candPerFrame * 4), "cudaMalloc(path codes)");
+        CK(h->node.ensure(B * g.candPerFrame * 2 + 16), "cudaMalloc(node labels)");
+        CK(h->candCount.ensure(B * g.nlevels * 4), "cudaMalloc(candidate counts)");
+        CK(h->lvKp.ensure(B * g.kpCapPerFrame * 4), "cudaMalloc(level keypoints)");
+        CK(h->lvCount.ensure(B * g.nlevels * 4), "cudaMalloc(level counts)");
+        CK(h->status.ensure(256), "cudaMalloc(status)");
+        CK(cudaMemset(h->status.p, 0, 256), "cudaMemset(status)");
+        CK(h->outKp.ensure(B * g.kpCapPerFrame * sizeof(os1_kp_dev)), "cudaMalloc(keypoints)");
+        CK(h->outDesc.ensure(B * g.kpCapPerFrame * 32), "cudaMalloc(descriptors)");
+        CK(h->outCount.ensure(B * 4), "cudaMalloc(counts)");
+        const size_t hostBytes = B * g.kpCapPerFrame * (sizeof(os1_kp_dev) + 32) + B * 4 + 64;
+        if (hostBytes > h->hostOutBytes) {
+            if (h->hostOut) cudaFreeHost(h->hostOut);
+            h->hostOut = nullptr; h->hostOutBytes = 0;
+            CK(cudaMallocHost(&h->hostOut, hostBytes), "cudaMallocHost(outputs)");
+            h->hostOutBytes = hostBytes;
+        }
+        if (!h->hostStatus) CK(cudaMallocHost((void**)&h->hostStatus, 64), "cudaMallocHost(status)");
+        h->batchCap = nframes;
+    }
+    return OS1_OK;
+}
+
+int check_status(os1_orb* h, int st)
+{
+    if (!st) return OS1_OK;
+    std::string m = "device-side capacity error:";
+    if (st & OS1_ERR_NODE_OVERFLOW) m += " quadtree node table overflow;";
+    if (st & OS1_ERR_DEPTH) m += " quadtree deeper than path code;";
+    if (st & OS1_ERR_KP_OVERFLOW) m += " keypoint capacity exceeded;";
+    if (st & OS1_ERR_CELL_OVERFLOW) m += " FAST cell staging overflow;";
+    cudaMemsetAsync(h->status.p, 0, 4, h->stream);
+    return fail(h, OS1_E_CAPACITY, m);
+}
+
+// the four launches of one extraction over `nframes` frames whose level 0 is already on the device
+int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0Pitch, int nframes, os1_kp_dev* kp, uint8_t* desc,
+                 int cap, int* counts)
+{
+    const Geometry& g = h->geom;
+    DevPtrs d;
+    d.lvl0 = lvl0; d.lvl0FrameStride = lvl0Stride; d.lvl0Pitch = lvl0Pitch;
+    d.slab = (uint8_t*)h->slab.p;
+    d.rtab = (const int16_t*)h->rtab.p; d.ptab = (const uint32_t*)h->ptab.p;
+    d.cellCnt = (uint32_t*)h->cellCnt.p; d.stage = (uint32_t*)h->stage.p; d.cand = (uint32_t*)h->cand.p;
+    d.code = (uint32_t*)h->code.p; d.node = (uint16_t*)h->node.p; d.candCount = (uint32_t*)h->candCount.p;
+    d.lvKp = (uint32_t*)h->lvKp.p; d.lvCount = (uint32_t*)h->lvCount.p; d.status = (int*)h->status.p;
+    h->lastFrames = nframes; h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch;
+    CK(os1_launch_pyramid(h->plan, g, d, nframes, h->stream), "pyramid kernel");
+    CK(os1_launch_fast(g, d, nframes, h->stream), "FAST kernel");
+    CK(os1_launch_quadtree(g, d, nframes, h->maxQuota, h->maxCells, h->stream), "quadtree kernel");
+    CK(os1_launch_describe(g, d, nframes, kp, desc, cap, counts, h->stream), "describe kernel");
+    return OS1_OK;
+}
+
+bool tma_ok(const void* p, size_t pitch, size_t frameStride)
+{
+    return ((uintptr_t)p % 16 == 0) && (pitch % 16 == 0) && (frameStride % 16 == 0);
+}
+
+} // namespace
+
+extern "C" {
+
+int os1_orb_create(os1_orb** out, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int device)
+{
+    os1_orb* h = nullptr;
+    if (!out) return fail(nullptr, OS1_E_INVALID, "os1_orb_create: out is NULL");
+    *out = nullptr;
+    if (nfeatures < 1 || nlevels < 1 || !(scaleFactor > 1.0f)) return fail(nullptr, OS1_E_INVALID, "os1_orb_create: need nfeatures >= 1, nlevels >= 1, scaleFactor > 1");
+    if (nlevels > OS1_MAX_LEVELS) return fail(nullptr, OS1_E_UNSUPPORTED, "os1_orb_create: more than 12 pyramid levels");
+    if (iniThFAST < 1 || minThFAST < 1 || iniThFAST > 254 || minThFAST > 254)
+        return fail(nullptr, OS1_E_UNSUPPORTED, "os1_orb_create: FAST thresholds must lie in 1..254");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, OS1_E_CUDA, std::string("os1_orb_create: no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+    }
+    if (device < 0 || device >= ndev) return fail(nullptr, OS1_E_INVALID, "os1_orb_create: bad device ordinal");
+    h = new os1_orb();
+    h->nfeatures = nfeatures; h->nlevels = nlevels; h->iniTh = iniThFAST; h->minTh = minThFAST;
+    h->scaleFactor = scaleFactor;
+    h->device = device;
+    build_tables(h);
+    if (h->maxQuota > 4000) { delete h; return fail(nullptr, OS1_E_UNSUPPORTED, "os1_orb_create: more than 4000 features in one level"); }
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) {
+        delete h;
+        return cuda_fail(nullptr, e, "os1_orb_create");
+    }
+    h->stream = h->ownStream;
+    *out = h;
+    return OS1_OK;
+}
+
+int os1_orb_destroy(os1_orb* h)
+{
+    if (!h) return OS1_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    if (h->plan) os1_pyramid_plan_destroy(h->plan);
+    DevBuf* bufs[] = { &h->rtab, &h->ptab, &h->slab, &h->cellCnt, &h->stage, &h->cand, &h->code, &h->node, &h->candCount,
+                       &h->lvKp, &h->lvCount, &h->status, &h->outKp, &h->outDesc, &h->outCount };
+    for (DevBuf* b : bufs) b->release();
+    if (h->hostOut) cudaFreeHost(h->hostOut);
+    if (h->hostStatus) cudaFreeHost(h->hostStatus);
+    if (h->ownStream) cudaStreamDestroy(h->ownStream);
+    delete h;
+    return OS1_OK;
+}
+
+const char* os1_last_error(const os1_orb* h) { return h ? h->err.c_str() : t_err.c_str(); }
+
+int os1_orb_get_levels(const os1_orb* h) { return h ? h->nlevels : 0; }
+float os1_orb_get_scale_factor(const os1_orb* h) { return h ? (float)h->scaleFactor : 0.f; }
+
+int os1_orb_get_tables(const os1_orb* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2)
+{
+    if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
+    for (int i = 0; i < h->nlevels; i++) {
+        if (scale) scale[i] = h->scale[i];
+        if (inv_scale) inv_scale[i] = h->inv[i];
+        if (sigma2) sigma2[i] = h->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = h->invsigma2[i];
+    }
+    return OS1_OK;
+}
+
+int os1_orb_get_features_per_level(const os1_orb* h, int* quota)
+{
+    if (!h || !quota) return fail(nullptr, OS1_E_INVALID, "NULL argument");
+    for (int i = 0; i < h->nlevels; i++) quota[i] = h->quota[i];
+    return OS1_OK;
+}
+
+int os1_orb_max_keypoints(const os1_orb* h)
+{
+    if (!h) return 0;
+    // independent of the resolution: quota + 2 per level, or the 4*nIni nodes of the first pass (nIni <= 4 for
+    // aspect ratios up to 4.5:1)
+    int n = 0;
+    for (int l = 0; l < h->nlevels; l++) n += std::max(h->quota[l] + 2, 16) + 2;
+    return n;
+}
+
+int os1_orb_reserve(os1_orb* h, int rows, int cols, int max_frames)
+{
+    if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
+    if (rows <= 0 || cols <= 0 || max_frames <= 0) return fail(h, OS1_E_INVALID, "os1_orb_reserve: bad size");
+    return ensure(h, rows, cols, max_frames);
+}
+
+int os1_orb_set_stream(os1_orb* h, void* cuda_stream)
+{
+    if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
+    h->stream = cuda_stream ? (cudaStream_t)cuda_stream : h->ownStream;
+    return OS1_OK;
+}
+
+int os1_orb_launches_per_call(const os1_orb*) { return 4; }
+
+int os1_orb_synchronize(os1_orb* h)
+{
+    if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
+    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    if (!h->status.p) { CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize"); return OS1_OK; }
+    CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "read status");
+    CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    return check_status(h, h->hostStatus[0]);
+}
+
+int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int rows, int cols, size_t step, size_t frame_stride,
+                          int frames_on_device, os1_keypoint* kp, uint8_t* desc, int cap_per_frame, int* counts, int out_on_device)
+{
+    if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
+    if (nframes <= 0 || !frames || rows <= 0 || cols <= 0) return OS1_OK;       // empty input: outputs untouched (:910-911)
+    if (!kp || !desc || !counts || cap_per_frame <= 0) return fail(h, OS1_E_INVALID, "os1_orb_extract_batch: NULL output or zero capacity");
+    if (step < (size_t)cols || (nframes > 1 && frame_stride < step * (size_t)(rows - 1) + cols))
+        return fail(h, OS1_E_INVALID, "os1_orb_extract_batch: step/frame_stride smaller than the image");
+    int rc = ensure(h, rows, cols, nframes);
+    if (rc) return rc;
+    const Geometry& g = h->geom;
+    const LevelGeom& L0 = g.lv[0];
+    uint8_t* slab = (uint8_t*)h->slab.p;
+
+    // ---- level 0 --------------------------------------------------------------------------------------------
+    const uint8_t* lvl0; long long lvl0Stride; int lvl0Pitch;
+    if (frames_on_device && tma_ok(frames, step, frame_stride)) {
+        lvl0 = frames; lvl0Stride = (long long)frame_stride; lvl0Pitch = (int)step;      // read in place
+    } else {
+        // stage into the slab (host frames: this IS the upload; odd device layouts: one D2D copy)
+        cudaMemcpy3DParms p;
+        memset(&p, 0, sizeof(p));
+        p.srcPtr = make_cudaPitchedPtr((void*)frames, step, cols, frame_stride / step);
+        p.dstPtr = make_cudaPitchedPtr(slab + L0.off, L0.pitch, cols, g.slabBytes / L0.pitch);
+        p.extent = make_cudaExtent(cols, rows, nframes);
+        p.kind = frames_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+        if (nframes > 1 && (frame_stride % step != 0 || g.slabBytes % L0.pitch != 0)) {
+            for (int f = 0; f < nframes; f++)
+                CK(cudaMemcpy2DAsync(slab + (long long)f * g.slabBytes + L0.off, L0.pitch, frames + (size_t)f * frame_stride, step, cols, rows,
+                                     p.kind, h->stream), "upload frame");
+        } else if (nframes == 1) {
+            CK(cudaMemcpy2DAsync(slab + L0.off, L0.pitch, frames, step, cols, rows, p.kind, h->stream), "upload frame");
+        } else {
+            CK(cudaMemcpy3DAsync(&p, h->stream), "upload frames");
+        }
+        lvl0 = slab + L0.off; lvl0Stride = g.slabBytes; lvl0Pitch = L0.pitch;
+    }
+
+    // ---- kernels ----------------------------------------------------------------------------------------------
+    if (out_on_device) {
+        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, nframes, (os1_kp_dev*)kp, desc, cap_per_frame, counts);
+        if (rc) return rc;
+        if (!frames_on_device) return os1_orb_synchronize(h);      // the host image may be reused by the caller
+        return OS1_OK;
+    }
+    const int cap = g.kpCapPerFrame;
+    rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, nframes, (os1_kp_dev*)h->outKp.p, (uint8_t*)h->outDesc.p, cap, (int*)h->outCount.p);
+    if (rc) return rc;
+    // ---- results -> pinned mirror -> caller ---------------------------------------------------------------------
+    uint8_t* hb = (uint8_t*)h->hostOut;
+    const size_t kpBytes = (size_t)nframes * cap * sizeof(os1_kp_dev), dBytes = (size_t)nframes * cap * 32;
+    os1_kp_dev* hk = (os1_kp_dev*)hb;
+    uint8_t* hd = hb + kpBytes;
+    int* hc = (int*)(hd + dBytes);
+    CK(cudaMemcpyAsync(hc, h->outCount.p, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream), "download counts");
+    CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
+    if (nframes == 1) {
+        // one frame: wait for the count, then fetch only what was produced
+        CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+        const int n = std::min(hc[0], cap);
+        if (n > 0) {
+            CK(cudaMemcpyAsync(hk, h->outKp.p, (size_t)n * sizeof(os1_kp_dev), cudaMemcpyDeviceToHost, h->stream), "download keypoints");
+            CK(cudaMemcpyAsync(hd, h->outDesc.p, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
+        }
+    } else {
+        CK(cudaMemcpyAsync(hk, h->outKp.p, kpBytes, cudaMemcpyDeviceToHost, h->stream), "download keypoints");
+        CK(cudaMemcpyAsync(hd, h->outDesc.p, dBytes, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
+    }
+    CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    rc = check_status(h, h->hostStatus[0]);
+    if (rc) return rc;
+    for (int f = 0; f < nframes; f++) {
+        const int n = hc[f];
+        if (n > cap_per_frame) return fail(h, OS1_E_CAPACITY, "os1_orb_extract: caller capacity smaller than the keypoint count (see os1_orb_max_keypoints)");
+        counts[f] = n;
+        memcpy(kp + (size_t)f * cap_per_frame, hk + (size_t)f * cap, (size_t)n * sizeof(os1_keypoint));
+        memcpy(desc + (size_t)f * cap_per_frame * 32, hd + (size_t)f * cap * 32, (size_t)n * 32);
+    }
+    return OS1_OK;
+}
+
+int os1_orb_extract(os1_orb* h, const uint8_t* image, int rows, int cols, size_t step, os1_keypoint* kp, int kp_cap, uint8_t* desc, int* n)
+{
+    if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
+    if (!image || rows <= 0 || cols <= 0) return OS1_OK;            // if(_image.empty()) return;  (:910-911)
+    if (!n) return fail(h, OS1_E_INVALID, "os1_orb_extract: n is NULL");
+    return os1_orb_extract_batch(h, image, 1, rows, cols, step, step * (size_t)rows, 0, kp, desc, kp_cap, n, 0);
+}
+
+// ---- stage accessors ------------------------------------------------------------------------------------------
+int os1_orb_level_size(const os1_orb* h, int level, int* w, int* hh)
+{
+    if (!h || !h->haveGeom || level < 0 || level >= h->nlevels) return fail(nullptr, OS1_E_INVALID, "os1_orb_level_size: no geometry yet or bad level");
+    if (w) *w = h->geom.lv[level].w;
+    if (hh) *hh = h->geom.lv[level].h;
+    return OS1_OK;
+}
+
+int os1_orb_get_pyramid_level(os1_orb* h, int frame, int level, uint8_t* out_host)
+{
+    if (!h || !h->haveGeom || level < 0 || level >= h->nlevels || frame < 0 || frame >= h->lastFrames || !out_host)
+        return fail(h, OS1_E_INVALID, "os1_orb_get_pyramid_level: bad argument");
+    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    const LevelGeom& L = h->geom.lv[level];
+    const uint8_t* src; size_t pitch;
+    if (level == 0) { src = h->lastLvl0 + (long long)frame * h->lastLvl0Stride; pitch = h->lastLvl0Pitch; }
+    else { src = (uint8_t*)h->slab.p + (long long)frame * h->geom.slabBytes + L.off; pitch = L.pitch; }
+    CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    CK(cudaMemcpy2D(out_host, L.w, src, pitch, L.w, L.h, cudaMemcpyDeviceToHost), "download level");
+    return OS1_OK;
+}
+
+static int fetch_packed(os1_orb* h, const uint32_t* dev, int n, int32_t* xys, int addBorder)
+{
+    std::vector<uint32_t> tmp(std::max(n, 1));
+    if (n > 0) CK(cudaMemcpy(tmp.data(), dev, (size_t)n * 4, cudaMemcpyDeviceToHost), "download");
+    for (int i = 0; i < n; i++) {
+        xys[3 * i] = OS1_X(tmp[i]) + addBorder; xys[3 * i + 1] = OS1_Y(tmp[i]) + addBorder; xys[3 * i + 2] = OS1_S(tmp[i]);
+    }
+    return OS1_OK;
+}
+
+int os1_orb_get_candidates(os1_orb* h, int frame, int level, int32_t* xys, int cap, int* n)
+{
+    if (!h || !h->haveGeom || level < 0 || level >= h->nlevels || frame < 0 || frame >= h->lastFrames || !n)
+        return fail(h, OS1_E_INVALID, "os1_orb_get_candidates: bad argument");
+    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    uint32_t cnt = 0;
+    CK(cudaMemcpy(&cnt, (uint32_t*)h->candCount.p + (size_t)frame * h->nlevels + level, 4, cudaMemcpyDeviceToHost), "download count");
+    *n = (int)cnt;
+    if (!xys) return OS1_OK;
+    if ((int)cnt > cap) return fail(h, OS1_E_CAPACITY, "os1_orb_get_candidates: cap too small");
+    return fetch_packed(h, (uint32_t*)h->cand.p + (size_t)frame * h->geom.candPerFrame + h->geom.lv[level].candOff, (int)cnt, xys, 0);
+}
+
+int os1_orb_get_level_keypoints(os1_orb* h, int frame, int level, int32_t* xys, int cap, int* n)
+{
+    if (!h || !h->haveGeom || level < 0 || level >= h->nlevels || frame < 0 || frame >= h->lastFrames || !n)
+        return fail(h, OS1_E_INVALID, "os1_orb_get_level_keypoints: bad argument");
+    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    uint32_t cnt = 0;
+    CK(cudaMemcpy(&cnt, (uint32_t*)h->lvCount.p + (size_t)frame * h->nlevels + level, 4, cudaMemcpyDeviceToHost), "download count");
+    *n = (int)cnt;
+    if (!xys) return OS1_OK;
+    if ((int)cnt > cap) return fail(h, OS1_E_CAPACITY, "os1_orb_get_level_keypoints: cap too small");
+    return fetch_packed(h, (uint32_t*)h->lvKp.p + (size_t)frame * h->geom.kpCapPerFrame + h->geom.lv[level].kpOff, (int)cnt, xys, OS1_BORDER);
+}
+
+// ---- Hamming ----------------------------------------------------------------------------------------------------
+int os1_descriptor_distance(const uint8_t* a, const uint8_t* b)
+{
+    uint32_t pa[8], pb[8];
+    memcpy(pa, a, 32); memcpy(pb, b, 32);
+    int d = 0;
+    for (int i = 0; i < 8; i++) d += __builtin_popcount(pa[i] ^ pb[i]);
+    return d;
+}
+
+static int sm_count(int device)
+{
+    static std::mutex mu;
+    static int cache[64];
+    std::lock_guard<std::mutex> lk(mu);
+    if (device < 0 || device >= 64) return 148;
+    if (!cache[device]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0) n = 148;
+        cache[device] = n;
+    }
+    return cache[device];
+}
+
+int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist,
+                     int on_device, int device, void* cuda_stream)
+{
+    os1_orb* h = nullptr;
+    if (nA < 0 || nB < 0 || (nA > 0 && (!A || !best_idx || !best_dist || !second_dist)) || (nB > 0 && !B))
+        return fail(nullptr, OS1_E_INVALID, "os1_hamming_knn2: bad argument");
+    if (nA == 0) return OS1_OK;
+    CK(cudaSetDevice(device), "cudaSetDevice (no CPU fallback)");
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    const int nSplit = os1_hamming_splits(nA, nB, sm_count(device));
+    uint64_t* scratch = nullptr;
+    CK(cudaMallocAsync((void**)&scratch, (size_t)nSplit * nA * 8, s), "cudaMallocAsync(hamming partials)");
+    int rc = OS1_OK;
+    if (on_device) {
+        cudaError_t e = os1_launch_hamming_knn2_splits(A, nA, B, nB, best_idx, best_dist, second_dist, scratch, nSplit, s);
+        cudaFreeAsync(scratch, s);
+        if (e != cudaSuccess) return cuda_fail(nullptr, e, "hamming kernel");
+        return rc;
+    }
+    uint8_t *dA = nullptr, *dB = nullptr; int* dOut = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&dA, (size_t)nA * 32, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&dB, (size_t)std::max(nB, 1) * 32, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&dOut, (size_t)nA * 12, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dA, A, (size_t)nA * 32, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess && nB > 0) e = cudaMemcpyAsync(dB, B, (size_t)nB * 32, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = os1_launch_hamming_knn2_splits(dA, nA, dB, nB, dOut, dOut + nA, dOut + 2 * nA, scratch, nSplit, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(best_idx, dOut, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(best_dist, dOut + nA, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(second_dist, dOut + 2 * nA, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
+    if (dA) cudaFreeAsync(dA, s);
+    if (dB) cudaFreeAsync(dB, s);
+    if (dOut) cudaFreeAsync(dOut, s);
+    cudaFreeAsync(scratch, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "os1_hamming_knn2");
+    return OS1_OK;
+}
+
+int os1_hamming_window(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, int32_t* best_idx,
+                       int32_t* best_dist, int32_t* second_dist, int on_device, int device, void* cuda_stream)
+{
+    os1_orb* h = nullptr;
+    if (nA < 0 || nB < 0 || (nA > 0 && (!A || !ptr || !best_idx || !best_dist || !second_dist)))
+        return fail(nullptr, OS1_E_INVALID, "os1_hamming_window: bad argument");
+    if (nA == 0) return OS1_OK;
+    CK(cudaSetDevice(device), "cudaSetDevice (no CPU fallback)");
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    if (on_device) {
+        cudaError_t e = os1_launch_hamming_window(A, nA, B, ptr, cand, best_idx, best_dist, second_dist, s);
+        if (e != cudaSuccess) return cuda_fail(nullptr, e, "hamming window kernel");
+        return OS1_OK;
+    }
+    const int total = ptr[nA];
+    if (total < 0) return fail(nullptr, OS1_E_INVALID, "os1_hamming_window: ptr is not a prefix sum");
+    for (int i = 0; i < nA; i++)
+        if (ptr[i] > ptr[i + 1]) return fail(nullptr, OS1_E_INVALID, "os1_hamming_window: ptr is not monotone");
+    for (int k = 0; k < total; k++)
+        if (cand[k] < 0 || cand[k] >= nB) return fail(nullptr, OS1_E_INVALID, "os1_hamming_window: candidate index out of range");
+    uint8_t *dA = nullptr, *dB = nullptr; int *dOut = nullptr, *dPtr = nullptr, *dCand = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&dA, (size_t)nA * 32, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&dB, (size_t)std::max(nB, 1) * 32, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&dOut, (size_t)nA * 12, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&dPtr, (size_t)(nA + 1) * 4, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void**)&dCand, (size_t)std::max(total, 1) * 4, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dA, A, (size_t)nA * 32, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess && nB > 0) e = cudaMemcpyAsync(dB, B, (size_t)nB * 32, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dPtr, ptr, (size_t)(nA + 1) * 4, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess && total > 0) e = cudaMemcpyAsync(dCand, cand, (size_t)total * 4, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = os1_launch_hamming_window(dA, nA, dB, dPtr, dCand, dOut, dOut + nA, dOut + 2 * nA, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(best_idx, dOut, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(best_dist, dOut + nA, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(second_dist, dOut + 2 * nA, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
+    void* frees[] = { dA, dB, dOut, dPtr, dCand };
+    for (void* p : frees) if (p) cudaFreeAsync(p, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "os1_hamming_window");
+    return OS1_OK;
+}
+
+} // extern "C"

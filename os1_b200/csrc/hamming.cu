@@ -1,0 +1,140 @@
+// K6 — batched Hamming consumer (replaces the scalar ORBmatcher::DescriptorDistance, src/ORBmatcher.cc:1605-1621,
+// inside the scan loops of SearchForInitialization :431-452 and SearchByProjection :1360-1376, :79-107).
+//
+// 256-bit descriptors are 8 x u32; a distance is 8 XOR + 8 POPC (not a dense contraction: no tensor cores).
+// The scan loops keep (best, second best, index of best) with strict '<' while walking candidates in list
+// order, i.e. first-seen wins ties and "second" is the second-smallest VALUE of the multiset.  Both are
+// order statistics of the keys  k = dist << 20 | position :   best = min k,  second = min over max(k, best-so-far),
+// which turns the branchy scan into three integer min/max per pair and merges exactly across partitions:
+//      best' = min(b1, b2),   second' = min(max(b1, b2), s1, s2).
+//
+// knn2 (all pairs, config 4 of BASELINE.json): thread = one row of A held in registers, B streamed through
+// shared memory in 256-descriptor tiles read as broadcast uint4; B is split over blockIdx.y so that a 2000x2000
+// problem fills the GPU; the per-split partials go through a scratch array and a small merge kernel.
+// window (CSR candidate lists, what Frame::GetFeaturesInArea returns, src/Frame.cc:209-262): one warp per row.
+#include "os1_internal.cuh"
+#include <climits>
+
+#define HM_ROWS 128
+#define HM_TILE 256
+#define HM_POSBITS 20
+#define HM_POSMASK ((1u << HM_POSBITS) - 1)
+#define HM_EMPTY 0xFFFFFFFFu
+
+namespace {
+
+__device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) +
+           __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// partial[split * nA + row] = { bestKey, secondKey } with positions relative to the split start
+__global__ void __launch_bounds__(HM_ROWS) hamming_knn2_partial(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B, int nB,
+                                                                 int splitLen, uint2* __restrict__ partial)
+{
+    __shared__ uint4 tile[HM_TILE * 2];
+    const int row = blockIdx.x * HM_ROWS + threadIdx.x;
+    const int jb = blockIdx.y * splitLen, je = min(nB, jb + splitLen);
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+    if (row < nA) { a0 = __ldg(A + 2 * row); a1 = __ldg(A + 2 * row + 1); }
+    unsigned best = HM_EMPTY, second = HM_EMPTY;
+    for (int t0 = jb; t0 < je; t0 += HM_TILE) {
+        const int cnt = min(HM_TILE, je - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < cnt * 2; i += HM_ROWS) tile[i] = __ldg(B + 2 * (long long)t0 + i);
+        __syncthreads();
+        const unsigned base = (unsigned)(t0 - jb);
+#pragma unroll 4
+        for (int j = 0; j < cnt; j++) {
+            const unsigned k = ((unsigned)dist256(a0, a1, tile[2 * j], tile[2 * j + 1]) << HM_POSBITS) | (base + j);
+            second = min(second, max(k, best));
+            best = min(best, k);
+        }
+    }
+    if (row < nA) partial[(long long)blockIdx.y * nA + row] = make_uint2(best, second);
+}
+
+__global__ void hamming_knn2_merge(const uint2* __restrict__ partial, int nA, int nSplit, int splitLen, int* bestIdx, int* bestDist,
+                                   int* secondDist)
+{
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nA) return;
+    int bd = INT_MAX, bi = -1, sd = INT_MAX;
+    for (int s = 0; s < nSplit; s++) {                      // ascending index ranges: the earlier split wins ties
+        const uint2 p = partial[(long long)s * nA + row];
+        if (p.x == HM_EMPTY) continue;
+        const int d = (int)(p.x >> HM_POSBITS), i = s * splitLen + (int)(p.x & HM_POSMASK);
+        const int d2 = p.y == HM_EMPTY ? INT_MAX : (int)(p.y >> HM_POSBITS);
+        if (d < bd) { sd = min(bd, d2); bd = d; bi = i; }
+        else sd = min(sd, d);
+    }
+    bestIdx[row] = bi; bestDist[row] = bd; secondDist[row] = sd;
+}
+
+__global__ void __launch_bounds__(128) hamming_window_kernel(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B,
+                                                             const int* __restrict__ ptr, const int* __restrict__ cand, int* bestIdx,
+                                                             int* bestDist, int* secondDist)
+{
+    const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= nA) return;
+    const uint4 a0 = __ldg(A + 2 * row), a1 = __ldg(A + 2 * row + 1);
+    const int p0 = ptr[row], p1 = ptr[row + 1];
+    unsigned best = HM_EMPTY, second = HM_EMPTY;
+    for (int k = p0 + lane; k < p1; k += 32) {
+        const int j = __ldg(cand + k);
+        const unsigned key = ((unsigned)dist256(a0, a1, __ldg(B + 2 * (long long)j), __ldg(B + 2 * (long long)j + 1)) << HM_POSBITS) |
+                             (unsigned)(k - p0);
+        second = min(second, max(key, best));
+        best = min(best, key);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned ob = __shfl_xor_sync(0xffffffffu, best, o), os = __shfl_xor_sync(0xffffffffu, second, o);
+        second = min(min(second, os), max(best, ob));
+        best = min(best, ob);
+    }
+    if (lane == 0) {
+        if (best == HM_EMPTY) { bestIdx[row] = -1; bestDist[row] = INT_MAX; secondDist[row] = INT_MAX; }
+        else {
+            bestIdx[row] = cand[p0 + (int)(best & HM_POSMASK)];
+            bestDist[row] = (int)(best >> HM_POSBITS);
+            secondDist[row] = second == HM_EMPTY ? INT_MAX : (int)(second >> HM_POSBITS);
+        }
+    }
+}
+
+} // namespace
+
+// number of B partitions used for an nA x nB problem on a GPU with `sms` SMs
+int os1_hamming_splits(int nA, int nB, int sms)
+{
+    const int rowBlocks = (nA + HM_ROWS - 1) / HM_ROWS;
+    int s = (2 * sms + rowBlocks - 1) / rowBlocks;            // aim at ~2 CTAs per SM
+    const int maxS = (nB + HM_TILE - 1) / HM_TILE;             // at least one tile per split
+    if (s > maxS) s = maxS;
+    if (s < 1) s = 1;
+    return s;
+}
+
+cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8_t* B, int nB, int* bestIdx, int* bestDist,
+                                           int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s)
+{
+    if (nA <= 0) return cudaSuccess;
+    int splitLen = (nB + nSplit - 1) / nSplit;
+    splitLen = ((splitLen + HM_TILE - 1) / HM_TILE) * HM_TILE;
+    if (splitLen < HM_TILE) splitLen = HM_TILE;
+    if (splitLen > (int)HM_POSMASK) return cudaErrorInvalidValue;
+    dim3 grid((nA + HM_ROWS - 1) / HM_ROWS, nSplit);
+    hamming_knn2_partial<<<grid, HM_ROWS, 0, s>>>((const uint4*)A, nA, (const uint4*)B, nB, splitLen, (uint2*)scratch);
+    hamming_knn2_merge<<<(nA + 127) / 128, 128, 0, s>>>((const uint2*)scratch, nA, nSplit, splitLen, bestIdx, bestDist, secondDist);
+    return cudaGetLastError();
+}
+
+cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, int* bestIdx,
+                                      int* bestDist, int* secondDist, cudaStream_t s)
+{
+    if (nA <= 0) return cudaSuccess;
+    hamming_window_kernel<<<(nA + 3) / 4, 128, 0, s>>>((const uint4*)A, nA, (const uint4*)B, ptr, cand, bestIdx, bestDist, secondDist);
+    return cudaGetLastError();
+}

@@ -1,0 +1,102 @@
+// os1_b200 — internal declarations shared by the CUDA translation units (sm_100a only).
+//
+// Geometry mirrors the reference extractor (paths relative to the os1 tree):
+//   level sizes            src/ORBextractor.cc:976
+//   FAST cell grid         src/ORBextractor.cc:807-844
+//   quadtree roots/quotas  src/ORBextractor.cc:467-478, :575-595
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+
+#define OS1_MAX_LEVELS 12
+#define OS1_EDGE 19          // EDGE_THRESHOLD  (ORBextractor.cc:80)
+#define OS1_BORDER 16        // minBorderX = EDGE_THRESHOLD-3 (:807)
+#define OS1_PATH_BITS 12     // quadtree depth representable in a path code (level sides <= 4096 px)
+#define FAST_G 4             // FAST cells per CTA (fast.cu)
+
+// packed candidate / kept keypoint: x | y<<12 | score<<24  (x,y relative to (OS1_BORDER,OS1_BORDER))
+#define OS1_PACK_XYS(x, y, s) ((uint32_t)(x) | ((uint32_t)(y) << 12) | ((uint32_t)(s) << 24))
+#define OS1_X(p) ((int)((p) & 0xFFFu))
+#define OS1_Y(p) ((int)(((p) >> 12) & 0xFFFu))
+#define OS1_S(p) ((int)((p) >> 24))
+
+struct LevelGeom {
+    int w, h;               // level image size
+    int pitch;              // bytes per row inside the pyramid slab (multiple of 16)
+    long long off;          // byte offset of the level inside one frame's slab
+    // FAST cell grid
+    int nCols, nRows, wCell, hCell;
+    int maxBX, maxBY;       // maxBorderX/Y = w-16, h-16
+    int cellOff;            // first cell of this level in per-frame cell arrays
+    int nCells;
+    int cellCap;            // staging slots per cell
+    long long candOff;      // first slot of this level in the per-frame staging / cand / code / node arrays
+    int candCap;            // nCells * cellCap
+    int groupOff;           // first FAST work group (CTA) of this level
+    int groupsPerRow;       // CTAs per cell row
+    // quadtree
+    int W, H;               // maxBorder - minBorder
+    int nIni, quota;
+    int xsOff, ysOff;       // offsets (u32) of the spread path tables of this level
+    int kpOff, kpCap;       // kept-keypoint slots of this level inside a frame
+    // resize tables for this level as DESTINATION (level >= 1): entries {ofs, c0, c1}
+    int rxOff, ryOff;
+    float scale;            // mvScaleFactor[level]
+    float kpSize;           // (float)(int)(31 * scale)
+};
+
+struct Geometry {
+    int nlevels;
+    int rows, cols;
+    int iniTh, minTh;
+    int cellsPerFrame;
+    int groupsPerFrame;
+    int kpCapPerFrame;          // sum of kpCap
+    long long candPerFrame;     // sum of candCap
+    long long slabBytes;        // pyramid slab bytes per frame
+    LevelGeom lv[OS1_MAX_LEVELS];
+};
+
+// per-call device pointers
+struct DevPtrs {
+    const uint8_t* lvl0;        // level-0 pixels (user buffer or slab)
+    long long lvl0FrameStride;  // bytes between frames of level 0
+    int lvl0Pitch;
+    uint8_t* slab;              // pyramid slabs (levels >= 1; level 0 too when staged)
+    const int16_t* rtab;        // resize tables, 4 x int16 per entry {ofs, c0, c1, pad}
+    const uint32_t* ptab;       // quadtree path tables
+    uint32_t* cellCnt;          // [frame][cell]
+    uint32_t* stage;            // [frame][candPerFrame]
+    uint32_t* cand;             // [frame][candPerFrame]  ordered candidates
+    uint32_t* code;             // [frame][candPerFrame]
+    uint16_t* node;             // [frame][candPerFrame]
+    uint32_t* candCount;        // [frame][level]
+    uint32_t* lvKp;             // [frame][kpCapPerFrame] packed kept keypoints, level-major
+    uint32_t* lvCount;          // [frame][level]
+    int* status;                // device-side error flags (bit field), one int
+};
+
+#define OS1_ERR_NODE_OVERFLOW 1
+#define OS1_ERR_DEPTH 2
+#define OS1_ERR_KP_OVERFLOW 4
+#define OS1_ERR_CELL_OVERFLOW 8
+
+// cv::KeyPoint layout (28 bytes): pt.x pt.y size angle response octave class_id
+struct os1_kp_dev { float x, y, size, angle, response; int octave, class_id; };
+
+// ---- launchers (one per kernel family) -----------------------------------------------------------
+struct PyramidPlan;   // host-side tile tables (pyramid.cu)
+PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH);
+void os1_pyramid_plan_destroy(PyramidPlan*);
+cudaError_t os1_launch_pyramid(PyramidPlan*, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
+cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
+cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes, int maxQuota, int maxCells, cudaStream_t s);
+cudaError_t os1_launch_describe(const Geometry& g, const DevPtrs& d, int nframes, os1_kp_dev* kp, uint8_t* desc, int capPerFrame,
+                                int* counts, cudaStream_t s);
+// Hamming: nSplit partitions of B; scratch holds nSplit * nA uint2 partials
+int os1_hamming_splits(int nA, int nB, int sms);
+cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8_t* B, int nB, int* bestIdx, int* bestDist,
+                                           int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s);
+cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, int* bestIdx,
+                                      int* bestDist, int* secondDist, cudaStream_t s);

@@ -1,0 +1,272 @@
+// K1 — fused scale-pyramid build (replaces ORBextractor::ComputePyramid, src/ORBextractor.cc:971-996).
+//
+// One launch builds levels 1..L-1 of every frame of the batch.  A CTA owns one tile of the COARSEST level and
+// the chain of source footprints below it: it pulls its level-0 footprint into shared memory with one TMA
+// tile load (cp.async.bulk.tensor, SASS UTMALDG), then resizes level by level inside shared memory with
+// cv::resize's INTER_LINEAR fixed-point arithmetic (11-bit coefficients) and stores
+// only the pixels it owns.  Level 0 is read once from HBM and every other level is written once; no level is
+// ever re-read from global memory.  The 19-px REFLECT_101 border of the reference (:986,:991) is not produced:
+// no later stage reads it.
+//
+// Ownership: tile column tx owns [b_l[tx], b_l[tx+1]) at level l, where b_{L-1}[i] = i*TW and
+// b_{l-1}[i] = first source tap of b_l[i].  The computed (shared-memory) range of a level is the owned range
+// plus the source footprint of the next level's computed range, i.e. a halo of at most ~2 px per level.
+#include "os1_internal.cuh"
+#include <vector>
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <cstdlib>
+
+namespace {
+
+struct PyrParams {
+    int nlevels;
+    int ntx, nty;
+    int boxBytes;
+    int barOff;
+    const uint8_t* dbgLvl0; long long dbgStride; int dbgPitch, dbgW, dbgH;
+    const int4* xt;              // [level][ntx]  {c0, c1, own0, own1}
+    const int4* yt;              // [level][nty]
+    const short4* rtab;          // resize tables {s0, s1, c0, c1}
+    uint8_t* slab;
+    long long slabBytes;
+    int smemOff[OS1_MAX_LEVELS];
+    int smemPitch[OS1_MAX_LEVELS];
+    int rxOff[OS1_MAX_LEVELS], ryOff[OS1_MAX_LEVELS];
+    long long lvOff[OS1_MAX_LEVELS];
+    int lvPitch[OS1_MAX_LEVELS];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int x, int y, int z)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+        : "memory");
+}
+
+template <bool USE_TMA>
+__global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PyrParams p)
+{
+    extern __shared__ __align__(128) uint8_t sm_raw[];
+    // TMA wants a 128-byte aligned destination: align by hand (the launcher allocates 128 spare bytes) and keep
+    // the mbarrier in the same dynamic block
+    uint8_t* sm = (uint8_t*)(((uintptr_t)sm_raw + 127) & ~(uintptr_t)127);
+    uint64_t& bar = *(uint64_t*)(sm + p.barOff);
+    const int tx = blockIdx.x, ty = blockIdx.y, frame = blockIdx.z;
+    const int tid = threadIdx.y * 32 + threadIdx.x;
+
+    int4 PX = p.xt[tx], PY = p.yt[ty];      // level-0 ranges
+    if (USE_TMA) {
+        if (tid == 0) {
+            mbar_init(&bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            mbar_expect_tx(&bar, (uint32_t)p.boxBytes);
+            tma_load_3d(sm + p.smemOff[0], &tmap, &bar, PX.x, PY.x, frame);
+        }
+        __syncthreads();
+        mbar_wait(&bar, 0);
+    } else {
+        // debug path (OS1_DEBUG_NOTMA=1): plain loads of the same box
+        const uint8_t* g0 = p.dbgLvl0 + (long long)frame * p.dbgStride;
+        const int bw = p.smemPitch[0], bh = p.boxBytes / p.smemPitch[0];
+        for (int i = tid; i < bw * bh; i += 256) {
+            int r = i / bw, c = i - r * bw;
+            int gx = PX.x + c, gy = PY.x + r;
+            sm[p.smemOff[0] + i] = (gx < p.dbgW && gy < p.dbgH) ? g0[(long long)gy * p.dbgPitch + gx] : 0;
+        }
+        __syncthreads();
+    }
+
+    uint8_t* slab = p.slab + (long long)frame * p.slabBytes;
+    for (int l = 1; l < p.nlevels; l++) {
+        const int4 X = p.xt[l * p.ntx + tx], Y = p.yt[l * p.nty + ty];
+        const int cw = X.y - X.x, ch = Y.y - Y.x;
+        const uint8_t* src = sm + p.smemOff[l - 1];
+        uint8_t* dst = sm + p.smemOff[l];
+        const int sp = p.smemPitch[l - 1], dp = p.smemPitch[l];
+        const short4* rx = p.rtab + p.rxOff[l];
+        const short4* ry = p.rtab + p.ryOff[l];
+        uint8_t* g = slab + p.lvOff[l];
+        const int gp = p.lvPitch[l];
+        for (int lx = threadIdx.x; lx < cw; lx += 32) {
+            const int gx = X.x + lx;
+            const short4 ex = __ldg(rx + gx);
+            const int a0 = ex.x - PX.x, a1 = ex.y - PX.x;
+            const int cx0 = ex.z, cx1 = ex.w;
+            const bool ownx = gx >= X.z && gx < X.w;
+            for (int ly = threadIdx.y; ly < ch; ly += 8) {
+                const int gy = Y.x + ly;
+                const short4 ey = __ldg(ry + gy);
+                const uint8_t* r0 = src + (ey.x - PY.x) * sp;
+                const uint8_t* r1 = src + (ey.y - PY.x) * sp;
+                const int H0 = r0[a0] * cx0 + r0[a1] * cx1;
+                const int H1 = r1[a0] * cx0 + r1[a1] * cx1;
+                const int v = ((((int)ey.z * (H0 >> 4)) >> 16) + (((int)ey.w * (H1 >> 4)) >> 16) + 2) >> 2;
+                dst[ly * dp + lx] = (uint8_t)v;
+                if (ownx && gy >= Y.z && gy < Y.w) g[(long long)gy * gp + gx] = (uint8_t)v;
+            }
+        }
+        PX = X; PY = Y;
+        __syncthreads();
+    }
+}
+
+} // namespace
+
+struct PyramidPlan {
+    int TW, TH, ntx, nty;
+    int4* d_xt = nullptr;
+    int4* d_yt = nullptr;
+    PyrParams prm;
+    int boxW, boxH;
+    size_t smemBytes;
+    CUresult (*encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                       const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+};
+
+// host copy of the taps of one axis for level l as destination (mirrors what api.cu uploads into rtab)
+void os1_host_resize_taps(int ssize, int dsize, bool vertical, std::vector<short>& s0, std::vector<short>& s1, std::vector<short>& c0,
+                          std::vector<short>& c1);
+
+static void build_axis(const Geometry& g, bool vertical, int T, int& nt, std::vector<int4>& tab, std::vector<int>& maxC)
+{
+    const int L = g.nlevels, top = L - 1;
+    auto size = [&](int l) { return vertical ? g.lv[l].h : g.lv[l].w; };
+    nt = (size(top) + T - 1) / T;
+    std::vector<std::vector<short> > S0(L), S1(L);
+    for (int l = 1; l < L; l++) {
+        std::vector<short> c0, c1;
+        os1_host_resize_taps(size(l - 1), size(l), vertical, S0[l], S1[l], c0, c1);
+    }
+    std::vector<std::vector<int> > b(L, std::vector<int>(nt + 1));
+    for (int i = 0; i <= nt; i++) b[top][i] = std::min(i * T, size(top));
+    for (int l = top; l >= 1; l--)
+        for (int i = 0; i <= nt; i++) {
+            int v = (i == 0) ? 0 : (i == nt || b[l][i] >= size(l)) ? size(l - 1) : (int)S0[l][b[l][i]];
+            if (i > 0) v = std::max(v, b[l - 1][i - 1]);
+            b[l - 1][i] = v;
+        }
+    tab.assign((size_t)L * nt, make_int4(0, 0, 0, 0));
+    maxC.assign(L, 0);
+    for (int t = 0; t < nt; t++) {
+        int c0 = b[top][t], c1 = b[top][t + 1];
+        for (int l = top; l >= 0; l--) {
+            // TMA tile loads fault ("illegal instruction") unless the innermost start coordinate is a multiple
+            // of 16 bytes (measured on B200, CUDA 12.9): the level-0 footprint starts on a 16-px boundary
+            if (l == 0 && !vertical) c0 &= ~15;
+            tab[(size_t)l * nt + t] = make_int4(c0, c1, b[l][t], b[l][t + 1]);
+            maxC[l] = std::max(maxC[l], c1 - c0);
+            if (l == 0) break;
+            int n0 = b[l - 1][t], n1 = b[l - 1][t + 1];
+            if (c1 > c0) {
+                n0 = std::min(n0, (int)S0[l][c0]);
+                n1 = std::max(n1, (int)S1[l][c1 - 1] + 1);
+            }
+            c0 = n0; c1 = n1;
+        }
+    }
+}
+
+PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
+{
+    PyramidPlan* P = new PyramidPlan();
+    P->TW = tileW; P->TH = tileH;
+    std::vector<int4> xt, yt;
+    std::vector<int> mw, mh;
+    build_axis(g, false, tileW, P->ntx, xt, mw);
+    build_axis(g, true, tileH, P->nty, yt, mh);
+    cudaMalloc(&P->d_xt, xt.size() * sizeof(int4));
+    cudaMalloc(&P->d_yt, yt.size() * sizeof(int4));
+    cudaMemcpy(P->d_xt, xt.data(), xt.size() * sizeof(int4), cudaMemcpyHostToDevice);
+    cudaMemcpy(P->d_yt, yt.data(), yt.size() * sizeof(int4), cudaMemcpyHostToDevice);
+    PyrParams& p = P->prm;
+    memset(&p, 0, sizeof(p));
+    p.nlevels = g.nlevels; p.ntx = P->ntx; p.nty = P->nty;
+    p.xt = P->d_xt; p.yt = P->d_yt;
+    P->boxW = (mw[0] + 15) & ~15;
+    P->boxH = mh[0];
+    p.boxBytes = P->boxW * P->boxH;
+    size_t off = 0;
+    for (int l = 0; l < g.nlevels; l++) {
+        p.smemOff[l] = (int)off;
+        p.smemPitch[l] = (l == 0) ? P->boxW : ((mw[l] + 3) & ~3);
+        off += (size_t)p.smemPitch[l] * mh[l];
+        off = (off + 127) & ~(size_t)127;
+        p.rxOff[l] = g.lv[l].rxOff; p.ryOff[l] = g.lv[l].ryOff;
+        p.lvOff[l] = g.lv[l].off; p.lvPitch[l] = g.lv[l].pitch;
+    }
+    p.slabBytes = g.slabBytes;
+    p.barOff = (int)off;
+    P->smemBytes = off + 16 + 128;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) {
+        // leave encode null; the launcher reports the failure
+        fn = nullptr;
+    }
+    P->encode = (decltype(P->encode))fn;
+    if (P->smemBytes > 48 * 1024)
+    {
+        cudaFuncSetAttribute(pyramid_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smemBytes);
+        cudaFuncSetAttribute(pyramid_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smemBytes);
+    }
+    return P;
+}
+
+void os1_pyramid_plan_destroy(PyramidPlan* P)
+{
+    if (!P) return;
+    cudaFree(P->d_xt); cudaFree(P->d_yt);
+    delete P;
+}
+
+cudaError_t os1_launch_pyramid(PyramidPlan* P, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s)
+{
+    if (g.nlevels < 2) return cudaSuccess;
+    if (!P->encode || P->boxW > 256 || P->boxH > 256 || P->smemBytes > 200 * 1024) return cudaErrorNotSupported;
+    CUtensorMap tmap;
+    cuuint64_t dims[3] = { (cuuint64_t)g.cols, (cuuint64_t)g.rows, (cuuint64_t)nframes };
+    cuuint64_t strides[2] = { (cuuint64_t)d.lvl0Pitch, (cuuint64_t)d.lvl0FrameStride };
+    cuuint32_t box[3] = { (cuuint32_t)P->boxW, (cuuint32_t)P->boxH, 1 };
+    cuuint32_t estr[3] = { 1, 1, 1 };
+    CUresult r = P->encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)d.lvl0, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+    PyrParams p = P->prm;
+    p.rtab = (const short4*)d.rtab;
+    p.slab = d.slab;
+    dim3 grid(P->ntx, P->nty, nframes), block(32, 8);
+    p.dbgLvl0 = d.lvl0; p.dbgStride = d.lvl0FrameStride; p.dbgPitch = d.lvl0Pitch; p.dbgW = g.cols; p.dbgH = g.rows;
+    static const bool noTma = getenv("OS1_DEBUG_NOTMA") != nullptr;
+    if (noTma) pyramid_kernel<false><<<grid, block, P->smemBytes, s>>>(tmap, p);
+    else pyramid_kernel<true><<<grid, block, P->smemBytes, s>>>(tmap, p);
+    return cudaGetLastError();
+}

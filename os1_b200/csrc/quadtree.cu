@@ -1,0 +1,374 @@
+// K3 — keypoint distribution (replaces ORBextractor::DistributeOctTree and ExtractorNode::DivideNode,
+// src/ORBextractor.cc:571-795, :513-569, plus the fix-up of :879-889 which the describe kernel applies).
+//
+// One CTA per (frame, level) runs the whole culling in rounds, without the reference's std::list:
+//   * prologue: exclusive scan of the per-cell counts written by K2 and an ordered gather of the staged
+//     candidates -> the reference's vToDistributeKeys order (cell-row-major, row-major inside a cell);
+//   * every candidate carries a PATH CODE: root index plus, for each depth, the (x>=mid, y>=mid) bits of
+//     DivideNode's split.  DivideNode splits x and y independently (halfX from the x range only, :515-516),
+//     so the bits come from two small per-level tables indexed by x and by y (built on the host with the
+//     reference's float arithmetic); the node a candidate belongs to at depth d is a prefix of its code;
+//   * a round = count the four children of every live (multi-key) node with warp-aggregated shared-memory
+//     atomics, decide which nodes split (all of them in a full pass, :626-697; largest-first until the count
+//     reaches N in the final phase, :708-769, by a shared-memory bitonic sort on (size, creation rank) and a
+//     prefix sum), give the children their creation ranks by prefix sums, and re-label the candidates;
+//   * single-key children and unsplit nodes become leaves keyed by (round, rank); the best response per leaf
+//     is an atomicMax on (response<<24 | ~index) so that the first maximum wins as in :784;
+//   * the leaves are sorted into std::list front-to-back order (:776): newest round first, newest rank first,
+//     roots in push_back order.
+// Tie rule for equal-size nodes: later-created first (DESIGN.md "canonical tie rule").
+#include "os1_internal.cuh"
+
+#define QT_THREADS 1024
+#define QT_DONE 0xFFFFu
+#define QT_LEAF 0x80000000u
+
+namespace {
+
+struct QtParams {
+    Geometry g;
+    DevPtrs d;
+    int maxNodes, maxLeaves, maxCells, sortCap;
+};
+
+__device__ __forceinline__ int block_scan_excl(int v, int* warpSums, int& total)
+{
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    __syncthreads();                 // protect warpSums from the previous call
+    if (lane == 31) warpSums[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int s = warpSums[lane];
+        int si = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, si, o);
+            if (lane >= o) si += t;
+        }
+        warpSums[lane] = si - s;     // exclusive warp offsets
+        if (lane == 31) warpSums[32] = si;
+    }
+    __syncthreads();
+    total = warpSums[32];
+    return warpSums[w] + inc - v;
+}
+
+// in-place bitonic sort of n64 (power of two) keys, descending when desc != 0
+__device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
+{
+    for (int k = 2; k <= n; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < n; i += QT_THREADS) {
+                int ixj = i ^ j;
+                if (ixj > i) {
+                    unsigned long long x = a[i], y = a[ixj];
+                    bool up = ((i & k) == 0) != desc;
+                    if ((x > y) == up) { a[i] = y; a[ixj] = x; }
+                }
+            }
+            __syncthreads();
+        }
+}
+
+__global__ void __launch_bounds__(QT_THREADS, 1) quadtree_kernel(const __grid_constant__ QtParams P)
+{
+    extern __shared__ __align__(16) uint8_t smraw[];
+    const Geometry& g = P.g;
+    const int level = blockIdx.x, frame = blockIdx.y;
+    const LevelGeom& L = g.lv[level];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int N = L.quota;
+    const int D = OS1_PATH_BITS;
+
+    // ---- shared memory carve-up ---------------------------------------------------------------------------
+    unsigned long long* sortBuf = (unsigned long long*)smraw;                 // sortCap
+    uint32_t* cellOffs = (uint32_t*)(sortBuf + P.sortCap);                     // maxCells + 1
+    uint32_t* slotCnt = cellOffs + P.maxCells + 1;                             // 4 * maxNodes
+    uint32_t* slotInfo = slotCnt + 4 * P.maxNodes;                             // 4 * maxNodes
+    uint32_t* liveSize = slotInfo + 4 * P.maxNodes;                            // maxNodes  (x2 buffers)
+    uint32_t* liveKey = liveSize + 2 * P.maxNodes;                             // maxNodes  (x2 buffers)
+    uint32_t* procPos = liveKey + 2 * P.maxNodes;                              // maxNodes
+    uint32_t* order = procPos + P.maxNodes;                                    // maxNodes
+    uint32_t* nzCum = order + P.maxNodes;                                      // maxNodes + 1
+    uint32_t* mzCum = nzCum + P.maxNodes + 1;                                  // maxNodes + 1
+    uint32_t* unsplitLeaf = mzCum + P.maxNodes + 1;                            // maxNodes
+    uint32_t* leafKey = unsplitLeaf + P.maxNodes;                              // maxLeaves
+    uint32_t* leafBest = leafKey + P.maxLeaves;                                // maxLeaves
+    int* warpSums = (int*)(leafBest + P.maxLeaves);                            // 33
+    __shared__ int s_leafCount, s_cut, s_err;
+
+    const long long fbase = (long long)frame * g.candPerFrame + L.candOff;
+    const uint32_t* stage = P.d.stage + fbase;
+    uint32_t* cand = P.d.cand + fbase;
+    uint32_t* code = P.d.code + fbase;
+    uint16_t* node = P.d.node + fbase;
+    const uint32_t* cellCnt = P.d.cellCnt + (long long)frame * g.cellsPerFrame + L.cellOff;
+    const uint32_t* xs = P.d.ptab + L.xsOff;
+    const uint32_t* ys = P.d.ptab + L.ysOff;
+    uint32_t* outKp = P.d.lvKp + (long long)frame * g.kpCapPerFrame + L.kpOff;
+
+    if (tid == 0) { s_leafCount = 0; s_err = 0; }
+
+    // ---- 0. scan of cell counts -------------------------------------------------------------------------------
+    int n;
+    {
+        int carry = 0;
+        for (int base = 0; base < L.nCells; base += QT_THREADS) {
+            int c = base + tid;
+            int v = (c < L.nCells) ? (int)cellCnt[c] : 0;
+            int tot;
+            int ex = block_scan_excl(v, warpSums, tot);
+            if (c < L.nCells) cellOffs[c] = carry + ex;
+            carry += tot;
+        }
+        n = carry;
+        if (tid == 0) { cellOffs[L.nCells] = n; P.d.candCount[frame * g.nlevels + level] = n; }
+    }
+    __syncthreads();
+
+    // ---- 1. ordered gather + path codes (warp per cell) ---------------------------------------------------------
+    for (int c = warp; c < L.nCells; c += QT_THREADS / 32) {
+        const int off = cellOffs[c], cnt = cellOffs[c + 1] - off;
+        const uint32_t* s = stage + (long long)c * L.cellCap;
+        for (int r = lane; r < cnt; r += 32) {
+            uint32_t v = s[r];
+            cand[off + r] = v;
+            code[off + r] = __ldg(xs + OS1_X(v)) | __ldg(ys + OS1_Y(v));
+        }
+    }
+    __syncthreads();
+
+    // ---- 2. roots (:584-617) ----------------------------------------------------------------------------------------
+    const int nIni = L.nIni;
+    for (int i = tid; i < 4 * P.maxNodes; i += QT_THREADS) slotCnt[i] = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += QT_THREADS) {
+        const int i = base + tid;
+        const bool valid = i < n;
+        const unsigned m = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+            const int r = code[i] >> (2 * D);
+            const unsigned grp = __match_any_sync(m, r);
+            if (lane == __ffs(grp) - 1) atomicAdd(&slotCnt[r], __popc(grp));
+        }
+    }
+    __syncthreads();
+    int E = 0, Lcount = 0;          // live multi-key nodes, lNodes.size()
+    {
+        // nIni is tiny: every thread walks the roots redundantly, thread 0 writes
+        int e = 0, lc = 0;
+        for (int r = 0; r < nIni; r++) {
+            const uint32_t c = slotCnt[r];
+            if (c == 0) continue;
+            lc++;
+            if (c == 1) {
+                if (tid == 0) { int id = s_leafCount++; leafKey[id] = (0xFFFFu << 16) | r; leafBest[id] = 0; slotInfo[r] = QT_LEAF | id; }
+            } else {
+                if (tid == 0) { liveSize[e] = c; liveKey[e] = r; slotInfo[r] = e; }
+                e++;
+            }
+        }
+        E = e; Lcount = lc;
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += QT_THREADS) {
+        const uint32_t info = slotInfo[code[i] >> (2 * D)];
+        if (info & QT_LEAF) { atomicMax(&leafBest[info & 0xFFFF], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i)); node[i] = QT_DONE; }
+        else node[i] = (uint16_t)info;
+    }
+    __syncthreads();
+
+    // ---- 3. rounds ------------------------------------------------------------------------------------------------------
+    int phase = 1, depth = 0, round = 0, buf = 0;
+    while (E > 0) {
+        round++;
+        uint32_t* curSize = liveSize + buf * P.maxNodes;
+        uint32_t* curKey = liveKey + buf * P.maxNodes;
+        uint32_t* newSize = liveSize + (buf ^ 1) * P.maxNodes;
+        uint32_t* newKey = liveKey + (buf ^ 1) * P.maxNodes;
+        if (depth + 1 > D) { if (tid == 0) atomicOr(P.d.status, OS1_ERR_DEPTH); break; }
+        const int shift = 2 * (D - (depth + 1));
+
+        // processing order: list order in a full pass (roots ascending, afterwards newest first);
+        // (size, creation rank) descending in the final phase (:716-717)
+        if (phase == 1) {
+            for (int j = tid; j < E; j += QT_THREADS) {
+                int p = (round == 1) ? j : E - 1 - j;
+                procPos[j] = p; order[p] = j;
+            }
+        } else {
+            int n2 = 1; while (n2 < E) n2 <<= 1;
+            for (int j = tid; j < n2; j += QT_THREADS)
+                sortBuf[j] = (j < E) ? (((unsigned long long)curSize[j] << 32) | ((unsigned long long)(curKey[j] & 0xFFFFu) << 16) | (unsigned)j) : 0ull;
+            __syncthreads();
+            bitonic_sort(sortBuf, n2, true);
+            for (int p = tid; p < E; p += QT_THREADS) {
+                int j = (int)(sortBuf[p] & 0xFFFFu);
+                order[p] = j; procPos[j] = p;
+            }
+        }
+        for (int i = tid; i < 4 * E; i += QT_THREADS) slotCnt[i] = 0;
+        __syncthreads();
+
+        // sweep A: children sizes
+        for (int base = 0; base < n; base += QT_THREADS) {
+            const int i = base + tid;
+            int nd = QT_DONE;
+            if (i < n) nd = node[i];
+            const bool valid = nd != QT_DONE;
+            const unsigned m = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const int slot = nd * 4 + ((code[i] >> shift) & 3);
+                const unsigned grp = __match_any_sync(m, slot);
+                if (lane == __ffs(grp) - 1) atomicAdd(&slotCnt[slot], __popc(grp));
+            }
+        }
+        __syncthreads();
+
+        // non-empty / multi-key children per node, cumulated in processing order
+        {
+            int carryN = 0, carryM = 0;
+            for (int base = 0; base < E; base += QT_THREADS) {
+                const int p = base + tid;
+                int nz = 0, mz = 0;
+                if (p < E) {
+                    const int j = order[p];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) { uint32_t c = slotCnt[4 * j + q]; nz += (c > 0); mz += (c > 1); }
+                }
+                int tn, tm;
+                int en = block_scan_excl(nz, warpSums, tn);
+                int em = block_scan_excl(mz, warpSums, tm);
+                if (p < E) { nzCum[p] = carryN + en; mzCum[p] = carryM + em; }
+                carryN += tn; carryM += tm;
+            }
+            if (tid == 0) { nzCum[E] = carryN; mzCum[E] = carryM; s_cut = E - 1; }
+        }
+        __syncthreads();
+        if (phase == 2) {
+            // first processing position at which the node count reaches N (:762)
+            for (int p = tid; p < E; p += QT_THREADS) {
+                const bool here = Lcount + (int)nzCum[p + 1] - (p + 1) >= N;
+                const bool before = p > 0 && (Lcount + (int)nzCum[p] - p >= N);
+                if (here && !before) s_cut = p;
+            }
+            __syncthreads();
+        }
+        const int nSplit = s_cut + 1;
+        const int Lnew = Lcount + (int)nzCum[nSplit] - nSplit;
+        const int newE = (int)mzCum[nSplit];
+        bool fin = (Lnew >= N) || (Lnew == Lcount) || (newE == 0);
+        int nextPhase = phase;
+        if (phase == 1 && !fin && Lnew + 3 * newE > N) nextPhase = 2;
+        if (!fin && newE > P.maxNodes) { fin = true; if (tid == 0) atomicOr(P.d.status, OS1_ERR_NODE_OVERFLOW); }
+
+        // children of split nodes; unsplit nodes turn into leaves as they are
+        for (int p = tid; p < E; p += QT_THREADS) {
+            const int j = order[p];
+            if (p < nSplit) {
+                int rank = nzCum[p], mi = mzCum[p];
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    const uint32_t c = slotCnt[4 * j + q];
+                    if (c == 0) continue;
+                    const uint32_t key = ((uint32_t)round << 16) | (uint32_t)rank;
+                    rank++;
+                    if (c == 1 || fin) {
+                        int id = atomicAdd(&s_leafCount, 1);
+                        if (id < P.maxLeaves) {
+                            leafKey[id] = ((0xFFFFu - (key >> 16)) << 16) | (0xFFFFu - (key & 0xFFFFu));
+                            leafBest[id] = 0;
+                        } else { id = 0; s_err = 1; }
+                        slotInfo[4 * j + q] = QT_LEAF | id;
+                        if (c > 1) mi++;
+                    } else {
+                        newSize[mi] = c; newKey[mi] = key;
+                        slotInfo[4 * j + q] = mi;
+                        mi++;
+                    }
+                }
+            } else {
+                int id = atomicAdd(&s_leafCount, 1);
+                const uint32_t key = curKey[j];
+                if (id < P.maxLeaves) {
+                    // roots keep push_back order and sort after everything else
+                    leafKey[id] = (key >> 16) == 0 ? ((0xFFFFu << 16) | key) : (((0xFFFFu - (key >> 16)) << 16) | (0xFFFFu - (key & 0xFFFFu)));
+                    leafBest[id] = 0;
+                } else { id = 0; s_err = 1; }
+                unsplitLeaf[j] = id;
+            }
+        }
+        __syncthreads();
+
+        // sweep B: re-label candidates / vote for the best response of finished leaves
+        for (int i = tid; i < n; i += QT_THREADS) {
+            const int nd = node[i];
+            if (nd == QT_DONE) continue;
+            if ((int)procPos[nd] >= nSplit) {
+                atomicMax(&leafBest[unsplitLeaf[nd]], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
+                node[i] = QT_DONE;
+            } else {
+                const uint32_t info = slotInfo[nd * 4 + ((code[i] >> shift) & 3)];
+                if (info & QT_LEAF) {
+                    atomicMax(&leafBest[info & 0xFFFF], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
+                    node[i] = QT_DONE;
+                } else node[i] = (uint16_t)info;
+            }
+        }
+        __syncthreads();
+        Lcount = Lnew;
+        if (fin) break;
+        E = newE; phase = nextPhase; depth++; buf ^= 1;
+    }
+    __syncthreads();
+
+    // ---- 4. leaves -> list order -> kept keypoints ------------------------------------------------------------------
+    int nLeaves = min(s_leafCount, P.maxLeaves);
+    if (s_err && tid == 0) atomicOr(P.d.status, OS1_ERR_NODE_OVERFLOW);
+    {
+        int n2 = 1; while (n2 < nLeaves) n2 <<= 1;
+        for (int j = tid; j < n2; j += QT_THREADS)
+            sortBuf[j] = (j < nLeaves) ? (((unsigned long long)leafKey[j] << 32) | leafBest[j]) : ~0ull;
+        __syncthreads();
+        bitonic_sort(sortBuf, n2, false);
+        if (nLeaves > L.kpCap) { if (tid == 0) atomicOr(P.d.status, OS1_ERR_KP_OVERFLOW); nLeaves = L.kpCap; }
+        for (int j = tid; j < nLeaves; j += QT_THREADS) {
+            const uint32_t best = (uint32_t)sortBuf[j];
+            const int idx = 0xFFFFFF - (best & 0xFFFFFF);
+            outKp[j] = cand[idx];
+        }
+        if (tid == 0) P.d.lvCount[frame * g.nlevels + level] = nLeaves;
+    }
+}
+
+} // namespace
+
+cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes, int maxQuota, int maxCells, cudaStream_t s)
+{
+    static_assert(sizeof(QtParams) < 4000, "kernel parameter block too large");
+    QtParams P;
+    P.g = g; P.d = d;
+    int maxIni = 1;
+    for (int l = 0; l < g.nlevels; l++) maxIni = max(maxIni, g.lv[l].nIni);
+    P.maxNodes = max(maxQuota, maxIni) + 8;
+    P.maxLeaves = max(maxQuota + 2, 4 * maxIni) + 8;
+    P.maxCells = maxCells;
+    int sc = 1; while (sc < max(P.maxNodes, P.maxLeaves)) sc <<= 1;
+    P.sortCap = sc;
+    size_t smem = (size_t)P.sortCap * 8 + (size_t)(P.maxCells + 1) * 4 + (size_t)P.maxNodes * 4 * (4 + 4 + 2 + 2 + 1 + 1 + 1 + 1 + 1) + 8 * 4 +
+                  (size_t)P.maxLeaves * 8 + 34 * 4;
+    if (smem > 220 * 1024 || P.maxNodes > 16000) return cudaErrorNotSupported;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    dim3 grid(g.nlevels, nframes);
+    quadtree_kernel<<<grid, QT_THREADS, smem, s>>>(P);
+    return cudaGetLastError();
+}
