@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""bench.py — ORB extraction throughput of the B200-native front end (frames/s), per the round contract.
+
+A step = one pass of the hot path (pyramid -> FAST -> quadtree -> orientation/descriptors) over one batch of
+synthetic 1280x720 frames, 1500 features (BASELINE.json configs[1]); frames are sharded by rank with no
+data-path collective (weak scaling).  `value` is measured with the batch resident in HBM, `e2e` through the
+C-ABI with pinned HOST buffers (H2D of the frames and D2H of keypoints+descriptors inside the timed region).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl ours|reference]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ROWS, COLS, NFEAT = 720, 1280, 1500
+PARAMS = (NFEAT, 1.2, 8, 20, 7)
+WORKLOAD = "1280x720 synthetic stream, nFeatures 1500, scale 1.2, 8 levels, FAST 20/7 (BASELINE.json configs[1])"
+
+
+def level_sizes(rows, cols, nlevels=8, sf=1.2):
+    s = np.float32(1.0); out = []
+    for l in range(nlevels):
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(cols) * inv)), int(np.rint(np.float32(rows) * inv))))
+        s = np.float32(float(s) * float(np.float32(sf)))
+    return out
+
+
+def algorithmic_bytes(rows, cols, nkp):
+    """bytes every stage must move when it reads its input once and writes its output once."""
+    px = [w * h for w, h in level_sizes(rows, cols)]
+    P = sum(px)
+    return {"pyramid": (P - px[-1]) + (P - px[0]), "fast": P, "quadtree": 0, "describe": (961 + 1369 + 32 + 60) * nkp,
+            "blur": 2 * P, "total": (P - px[-1]) + (P - px[0]) + P + 2 * P + (961 + 1369 + 32 + 60) * nkp}
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index; self.rows = []; self.stop = False; self.proc = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+                if self.stop:
+                    break
+        except Exception:
+            pass
+
+    def finish(self):
+        self.stop = True
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for i, nme in enumerate(names):
+                if len(r) > 3 + i and r[3 + i].lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))["hbm_gbs"], "measured"
+    return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    """The reference's own CPU implementation of the path on the host cores: oracle/_ref (the unmodified
+    ORBextractor.cc) when it was built, else the oracle port; one extractor per thread, all host threads."""
+    if rank != 0:
+        return
+    from oracle import pyoracle
+    from os1_b200 import synth
+    threads = os.cpu_count() or 1
+    nframes = max(threads, 8)                      # bounded sample per step
+    frames = synth.video(nframes, ROWS, COLS, seed=0)
+    use_ref = pyoracle.Reference.available(canon=False)
+    if use_ref:
+        exts = [pyoracle.Reference(*PARAMS, canon=False) for _ in range(threads)]
+        kind = "reference"
+
+        def step():
+            nxt = [0]; lock = threading.Lock(); tot = [0]
+
+            def work(e):
+                while True:
+                    with lock:
+                        f = nxt[0]; nxt[0] += 1
+                    if f >= nframes:
+                        return
+                    k, _ = e.extract(frames[f], cap=4096)
+                    with lock:
+                        tot[0] += len(k)
+            ts = [threading.Thread(target=work, args=(e,)) for e in exts]
+            [t.start() for t in ts]; [t.join() for t in ts]
+            return tot[0]
+    else:
+        kind = "port"
+
+        def step():
+            tot, _ = pyoracle.Oracle.extract_batch(frames, PARAMS, threads)
+            return tot
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    fps = args.steps * nframes / dt
+    sample = "%d frames per step on %d host threads, one extractor per thread (%s)" % (
+        nframes, threads, "oracle/_ref: unmodified reference ORBextractor.cc" if use_ref else "oracle port")
+    line = {"impl": "reference", "metric": "ORB frames/sec", "value": fps, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": {"workload": WORKLOAD, "frames_per_step": nframes},
+            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": kind, "sample": sample},
+            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_sample():
+    """Bounded CPU sample for the `cpu_baseline` object of our own line (rank 0, N=1)."""
+    from oracle import pyoracle
+    from os1_b200 import synth
+    threads = os.cpu_count() or 1
+    nframes = max(threads, 8)
+    frames = synth.video(nframes, ROWS, COLS, seed=0)
+    if pyoracle.Reference.available(canon=False):
+        kind = "reference"
+        exts = [pyoracle.Reference(*PARAMS, canon=False) for _ in range(threads)]
+
+        def run():
+            nxt = [0]; lock = threading.Lock()
+
+            def work(e):
+                while True:
+                    with lock:
+                        f = nxt[0]; nxt[0] += 1
+                    if f >= nframes:
+                        return
+                    e.extract(frames[f], cap=4096)
+            ts = [threading.Thread(target=work, args=(e,)) for e in exts]
+            [t.start() for t in ts]; [t.join() for t in ts]
+    else:
+        kind = "port"
+
+        def run():
+            pyoracle.Oracle.extract_batch(frames, PARAMS, threads)
+    run()
+    reps = 0; t0 = time.perf_counter()
+    while True:
+        run(); reps += 1
+        if time.perf_counter() - t0 > 10.0 or reps >= 20:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": reps * nframes / dt, "unit": "frames/s", "cores": threads, "kind": kind,
+            "sample": "%d x %d synthetic 720p frames, one extractor per thread, %d host threads, %.1f s" % (reps, nframes, threads, dt)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import os1_b200
+    from os1_b200 import synth
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    B = args.batch
+    frames_h = torch.from_numpy(synth.video(B, ROWS, COLS, seed=1000 + rank)).pin_memory()
+    frames_d = frames_h.to(dev, non_blocking=False)                       # resident in HBM before the timed region
+    ext = os1_b200.ORBextractor(*PARAMS, device=local_rank)
+    cap = ext.max_keypoints()
+    ext.reserve(ROWS, COLS, B)
+    stream = torch.cuda.current_stream(dev)
+    ext.set_stream(stream.cuda_stream)
+    kp_d = torch.empty((B, cap, 28), dtype=torch.uint8, device=dev)
+    desc_d = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
+    cnt_d = torch.zeros(B, dtype=torch.int32, device=dev)
+    kp_h = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory()
+    desc_h = torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()
+    cnt_h = torch.zeros(B, dtype=torch.int32).pin_memory()
+
+    def step_device():
+        ext.extract_batch_raw(frames_d.data_ptr(), B, ROWS, COLS, COLS, ROWS * COLS, True,
+                              kp_d.data_ptr(), desc_d.data_ptr(), cap, cnt_d.data_ptr(), True)
+
+    def step_e2e():
+        ext.extract_batch_raw(frames_h.data_ptr(), B, ROWS, COLS, COLS, ROWS * COLS, False,
+                              kp_h.data_ptr(), desc_h.data_ptr(), cap, cnt_h.data_ptr(), False)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- device-resident throughput (`value`) + per-kernel durations for the roofline
+    ext.set_timing(True)
+    for _ in range(args.warmup):
+        step_device()
+    ext.synchronize()
+    sampler = ClockSampler(local_rank); sampler.start()
+    barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    stage_ms = np.zeros(4)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+        stage_ms += ext.stage_times_ms()        # waits for this step's last event: steps are serialised anyway
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.finish()
+    ext.synchronize()
+    counts = cnt_d.cpu().numpy()
+    if dist is not None:
+        t = torch.tensor([ms], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+    ext.set_timing(False)
+
+    # ---- end to end through the C ABI with pinned host buffers
+    for _ in range(max(1, args.warmup // 2)):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([e2e_s], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX); e2e_s = float(t.item())
+    assert np.array_equal(cnt_h.numpy(), counts), "host and device paths disagree on keypoint counts"
+    nkp = int(counts.sum())
+
+    if rank != 0:
+        return
+    fps = world * B * args.steps / (ms * 1e-3)
+    e2e_fps = world * B * args.steps / e2e_s
+    # roofline of the dominant kernel
+    names = ["pyramid", "fast", "quadtree", "describe"]
+    alg = algorithmic_bytes(ROWS, COLS, nkp / B)
+    dom = int(np.argmax(stage_ms))
+    per_launch_ms = stage_ms / args.steps
+    peak, which = peaks()
+    dom_bytes = alg[names[dom]] * B
+    achieved = dom_bytes / (per_launch_ms[dom] * 1e-3) / 1e9
+    whole = alg["total"] * B / (ms / args.steps * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": names[dom] + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": None, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)" if which == "measured" else "fallback 6650 GB/s",
+            "algorithmic_bytes_per_launch": dom_bytes,
+            "kernel_ms_per_launch": {n: float(v) for n, v in zip(names, per_launch_ms)},
+            "whole_step_achieved_gbs": whole, "whole_step_frac": whole / peak}
+    line = {"metric": "ORB frames/sec", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp / B,
+                       "l2": "inputs larger than L2 (%d MB of frames per step per GPU, plus %d MB of pyramid)" % (
+                           B * ROWS * COLS >> 20, B * 1930000 >> 20),
+                       "parallelism": "frame-sharded, %d rank(s), no data-path collective" % world},
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(B * ROWS * COLS),
+                    "d2h_bytes_per_step": int(B * cap * 60 + B * 4 + 4)},
+            "gpu_launches": int(args.steps * ext.launches_per_call()),
+            "roofline": roof, "clocks": clocks}
+    if world == 1:
+        try:
+            line["cpu_baseline"] = cpu_baseline_sample()
+        except Exception as ex:           # the checker libraries are optional on the box; say so rather than fail the bench
+            line["cpu_baseline"] = {"value": None, "unit": "frames/s", "cores": 0, "kind": "port", "sample": "unavailable: %s" % ex}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=256, help="frames per step per GPU")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -83,6 +83,11 @@ int os1_orb_synchronize(os1_orb* h);
 int os1_orb_set_stream(os1_orb* h, void* cuda_stream);
 /* Number of kernels one extract call launches (for launch accounting). */
 int os1_orb_launches_per_call(const os1_orb* h);
+/* Measurement aid (no reference counterpart): with timing enabled every extract call brackets its four kernels
+ * (pyramid, FAST, quadtree, describe) with CUDA events on the handle's stream; os1_orb_get_stage_times waits for
+ * the last call and returns the four durations in milliseconds. */
+int os1_orb_set_timing(os1_orb* h, int enable);
+int os1_orb_get_stage_times(os1_orb* h, float* ms4);
 
 /* ---- stage accessors (parity tests; frame index refers to the last extract call) --------------------- */
 /* public mvImagePyramid (include/ORBextractor.h:245), without the never-read 19-px border: w*h bytes, packed. */

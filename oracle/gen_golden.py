@@ -1,0 +1,63 @@
+"""Generates tests/golden/*.npz — run in the build container, where cv2 4.13.0 and /root/reference exist.
+
+  primitives.npz : small seeded inputs with the outputs of the REAL OpenCV primitives (cv2.resize INTER_LINEAR,
+                   cv2.GaussianBlur 7x7 s=2 REFLECT_101, cv2 FAST 9_16 nonmax at 20 and 7, cv2.fastAtan2) — pins
+                   oracle/cv_exact.h to third-party arithmetic that is not vendored by the reference.
+  extract_*.npz  : keypoints + descriptors + per-level candidate counts produced by the UNMODIFIED reference
+                   ORBextractor.cc (oracle/_ref/libos1_ref_canon.so, canonical tie rule) on seeded synthetic frames,
+                   plus the count/difference seen with the stock glibc allocator build (libos1_ref.so).
+The frames themselves are regenerated from the seed by os1_b200/synth.py, so the fixtures stay small.
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from os1_b200 import synth  # noqa: E402
+from oracle import pyoracle  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def primitives():
+    import cv2
+    cv2.setNumThreads(1)
+    d = {"cv2_version": np.array(cv2.__version__)}
+    img = synth.frame(240, 320, 11)
+    d["img"] = img
+    for k, (dw, dh) in enumerate([(267, 200), (222, 167), (149, 112)]):
+        d["resize_%d" % k] = cv2.resize(img, (dw, dh), interpolation=cv2.INTER_LINEAR)
+    d["blur"] = cv2.GaussianBlur(img, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+    for th in (20, 7):
+        f = cv2.FastFeatureDetector_create(th, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+        d["fast_%d" % th] = np.array([(p.pt[0], p.pt[1], p.response) for p in f.detect(img)], np.int32).reshape(-1, 3)
+    rng = np.random.default_rng(5)
+    y = rng.integers(-3000000, 3000000, 4000).astype(np.float32)
+    x = rng.integers(-3000000, 3000000, 4000).astype(np.float32)
+    y[:4] = [0, -5, 0, 5]; x[:4] = [0, 0, -3, 5]
+    d["atan_y"] = y; d["atan_x"] = x
+    d["atan"] = np.array([cv2.fastAtan2(float(a), float(b)) for a, b in zip(y, x)], np.float32)
+    np.savez_compressed(os.path.join(OUT, "primitives.npz"), **d)
+
+
+def extraction():
+    for name, (h, w, nf, seed) in {"vga": (480, 640, 1000, 0), "720p": (720, 1280, 1500, 1), "small": (200, 260, 300, 4)}.items():
+        img = synth.frame(h, w, seed)
+        rc = pyoracle.Reference(nf, canon=True)
+        kp, desc = rc.extract(img, record=True)
+        ncand = np.array([len(rc.candidates(l)) for l in range(8)], np.int32)
+        rg = pyoracle.Reference(nf, canon=False)
+        kg, _ = rg.extract(img)
+        sc = set(map(tuple, kp[:, [0, 1, 5]].tolist())); sg = set(map(tuple, kg[:, [0, 1, 5]].tolist()))
+        np.savez_compressed(os.path.join(OUT, "extract_%s.npz" % name), h=h, w=w, nfeatures=nf, seed=seed, kp=kp, desc=desc,
+                            ncand=ncand, glibc_count=len(kg), glibc_only=len(sg - sc), canon_only=len(sc - sg),
+                            tables_scale=rc.tables()["scale"], tables_quota=rc.tables()["quota"], tables_umax=rc.tables()["umax"])
+        print(name, len(kp), "glibc build:", len(kg), "differs by", len(sg - sc), "/", len(sc - sg))
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    primitives()
+    extraction()

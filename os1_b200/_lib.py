@@ -26,6 +26,8 @@ SYMBOLS = [
     ("os1_orb_synchronize", _i, [_vp]),
     ("os1_orb_set_stream", _i, [_vp, _vp]),
     ("os1_orb_launches_per_call", _i, [_vp]),
+    ("os1_orb_set_timing", _i, [_vp, _i]),
+    ("os1_orb_get_stage_times", _i, [_vp, _vp]),
     ("os1_orb_level_size", _i, [_vp, _i, C.POINTER(_i), C.POINTER(_i)]),
     ("os1_orb_get_pyramid_level", _i, [_vp, _i, _i, _vp]),
     ("os1_orb_get_candidates", _i, [_vp, _i, _i, _vp, _i, C.POINTER(_i)]),

@@ -56,6 +56,9 @@ struct os1_orb {
     // pinned host mirrors for the host-buffer path
     void* hostOut = nullptr; size_t hostOutBytes = 0;
     int* hostStatus = nullptr;
+    // optional per-kernel timing (bench.py's roofline): events around the four launches of the last call
+    bool timing = false;
+    cudaEvent_t ev[5] = { nullptr, nullptr, nullptr, nullptr, nullptr };
 };
 
 namespace {
@@ -194,9 +197,12 @@ int build_geometry(os1_orb* h, int rows, int cols)
         v.W = v.maxBX - OS1_BORDER; v.H = v.maxBY - OS1_BORDER;
         const float width = (float)v.W, height = (float)v.H;
         v.nCols = (int)(width / 30.f); v.nRows = (int)(height / 30.f);   // :820-821
-        if (v.nCols < 1 || v.nRows < 1)
-            return fail(h, OS1_E_UNSUPPORTED, "image too small for this many pyramid levels (a level is below 62 px; the reference divides by zero there)");
-        v.wCell = (int)ceil(width / v.nCols); v.hCell = (int)ceil(height / v.nRows);   // :822-823
+        if (v.w < 1 || v.h < 1) return fail(h, OS1_E_UNSUPPORTED, "a pyramid level has zero size (cv::resize throws there)");
+        // A level narrower or lower than 62 px has no FAST cell row/column: the reference's cell loops do not run
+        // (:826,:837) and DistributeOctTree gets nothing, so the level is built but yields no keypoints.
+        const bool dead = v.nCols < 1 || v.nRows < 1;
+        if (dead) { v.nCols = v.nRows = 0; v.wCell = v.hCell = 1; v.W = std::max(v.W, 1); v.H = std::max(v.H, 1); }
+        else { v.wCell = (int)ceil(width / v.nCols); v.hCell = (int)ceil(height / v.nRows); }   // :822-823
         v.nCells = v.nCols * v.nRows;
         v.cellOff = cellOff; cellOff += v.nCells;
         v.cellCap = ((v.wCell + 1) / 2) * ((v.hCell + 1) / 2);
@@ -206,8 +212,9 @@ int build_geometry(os1_orb* h, int rows, int cols)
         v.groupsPerRow = (v.nCols + FAST_G - 1) / FAST_G;
         v.groupOff = groupOff; groupOff += v.groupsPerRow * v.nRows;
         h->maxCells = std::max(h->maxCells, v.nCells);
-        v.nIni = (int)roundf((float)v.W / v.H);                            // :575
+        v.nIni = dead ? 1 : (int)roundf((float)v.W / v.H);                // :575
         if (v.nIni < 1) return fail(h, OS1_E_UNSUPPORTED, "portrait images taller than 2:1 (the reference's nIni is 0 there)");
+        if (v.nIni > 4) return fail(h, OS1_E_UNSUPPORTED, "images wider than 4.5:1");
         v.quota = h->quota[l];
         v.xsOff = (int)ptab.size();
         { std::vector<uint32_t> t; build_path_table(v.W, v.nIni, true, t); ptab.insert(ptab.end(), t.begin(), t.end()); }
@@ -311,10 +318,16 @@ int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0
     d.code = (uint32_t*)h->code.p; d.node = (uint16_t*)h->node.p; d.candCount = (uint32_t*)h->candCount.p;
     d.lvKp = (uint32_t*)h->lvKp.p; d.lvCount = (uint32_t*)h->lvCount.p; d.status = (int*)h->status.p;
     h->lastFrames = nframes; h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch;
+    const bool t = h->timing;
+    if (t) CK(cudaEventRecord(h->ev[0], h->stream), "cudaEventRecord");
     CK(os1_launch_pyramid(h->plan, g, d, nframes, h->stream), "pyramid kernel");
+    if (t) CK(cudaEventRecord(h->ev[1], h->stream), "cudaEventRecord");
     CK(os1_launch_fast(g, d, nframes, h->stream), "FAST kernel");
+    if (t) CK(cudaEventRecord(h->ev[2], h->stream), "cudaEventRecord");
     CK(os1_launch_quadtree(g, d, nframes, h->maxQuota, h->maxCells, h->stream), "quadtree kernel");
+    if (t) CK(cudaEventRecord(h->ev[3], h->stream), "cudaEventRecord");
     CK(os1_launch_describe(g, d, nframes, kp, desc, cap, counts, h->stream), "describe kernel");
+    if (t) CK(cudaEventRecord(h->ev[4], h->stream), "cudaEventRecord");
     return OS1_OK;
 }
 
@@ -369,6 +382,7 @@ int os1_orb_destroy(os1_orb* h)
     for (DevBuf* b : bufs) b->release();
     if (h->hostOut) cudaFreeHost(h->hostOut);
     if (h->hostStatus) cudaFreeHost(h->hostStatus);
+    for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->ownStream) cudaStreamDestroy(h->ownStream);
     delete h;
     return OS1_OK;
@@ -423,6 +437,26 @@ int os1_orb_set_stream(os1_orb* h, void* cuda_stream)
 }
 
 int os1_orb_launches_per_call(const os1_orb*) { return 4; }
+
+int os1_orb_set_timing(os1_orb* h, int enable)
+{
+    if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
+    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    if (enable && !h->ev[0])
+        for (int i = 0; i < 5; i++) CK(cudaEventCreate(&h->ev[i]), "cudaEventCreate");
+    h->timing = enable != 0;
+    return OS1_OK;
+}
+
+int os1_orb_get_stage_times(os1_orb* h, float* ms4)
+{
+    if (!h || !ms4) return fail(h, OS1_E_INVALID, "os1_orb_get_stage_times: NULL argument");
+    if (!h->timing || !h->ev[0]) return fail(h, OS1_E_INVALID, "os1_orb_get_stage_times: timing is off");
+    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    CK(cudaEventSynchronize(h->ev[4]), "cudaEventSynchronize");
+    for (int i = 0; i < 4; i++) CK(cudaEventElapsedTime(&ms4[i], h->ev[i], h->ev[i + 1]), "cudaEventElapsedTime");
+    return OS1_OK;
+}
 
 int os1_orb_synchronize(os1_orb* h)
 {

@@ -122,6 +122,15 @@ class ORBextractor:
     def launches_per_call(self):
         return self._L.os1_orb_launches_per_call(self._h)
 
+    def set_timing(self, enable=True):
+        _lib.check(self._L.os1_orb_set_timing(self._h, int(enable)), self._h)
+
+    def stage_times_ms(self):
+        """Durations (ms) of the pyramid, FAST, quadtree and describe kernels of the last call."""
+        t = np.zeros(4, np.float32)
+        _lib.check(self._L.os1_orb_get_stage_times(self._h, _ptr(t)), self._h)
+        return t
+
     # ---- stage accessors (parity tests)
     def level_size(self, level):
         w, h = C.c_int(), C.c_int()
