@@ -7,7 +7,7 @@
  * in front of the reference's own include/, drop src/ORBextractor.cc from the build, link libos1_b200.so.
  *
  * Needs <opencv2/core/core.hpp> for cv::Mat / cv::KeyPoint / cv::InputArray / cv::OutputArray — the real OpenCV in
- * os1's build; the repo's tests compile it against the minimal shim under oracle/cvshim.
+ * os1's build; the repo's tests compile it against a minimal stand-in for those headers (test infrastructure).
  */
 #ifndef ORBEXTRACTOR_H
 #define ORBEXTRACTOR_H
