@@ -117,6 +117,30 @@ int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t
 int os1_hamming_window(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, int32_t* best_idx,
                        int32_t* best_dist, int32_t* second_dist, int on_device, int device, void* cuda_stream);
 
+/* os1_hamming_knn2 for callers that must not allocate.  This entry point has no counterpart in the reference
+ * (os1 has no GPU code and so no allocation policy to mirror); it exists for the hosts this library gets embedded in.
+ *
+ * Who needs it: a tracking thread with a per-frame deadline, where a cudaMalloc / cudaFree (or a pool growing under
+ * cudaMallocAsync) can take the driver's allocator lock or synchronise the device at an unpredictable moment; a
+ * process whose device memory was divided up front between components, where a late allocation may simply fail;
+ * a plug-in running inside a host application that forbids allocation on its worker threads.  os1_hamming_knn2
+ * obtains its per-call scratch from the stream-ordered allocator and is therefore not suitable for them.
+ *
+ * What it does differently: the scratch (one 8-byte partial result per row of A and per partition of B) is a fixed
+ * 1 MiB array inside the library's device image.  It is present on every GPU that loads the library, from load until
+ * the process exits.  The call performs no cudaMalloc, cudaFree, cudaMallocAsync or any other allocating call.
+ * A, B and the three outputs are DEVICE pointers on `device`, supplied by the caller; results are identical to
+ * os1_hamming_knn2 with on_device = 1.  The work is enqueued on cuda_stream (may be NULL) and not waited for.
+ *
+ * Limits: nA <= 4096 and nB <= 65536; anything larger returns OS1_E_CAPACITY and launches nothing.
+ * First use: the first call on a given device looks up the device address of the built-in array (a one-time
+ * runtime query, made with that device current).  Make that first call during start-up, before any stream capture.
+ * Sharing: all calls on one GPU use the same array, and it keeps whatever the previous call left in it.  Nothing needs
+ * clearing between calls (each call overwrites every entry it later reads), but two calls whose kernels can overlap on
+ * the same GPU — different streams, or different host threads — race on it and return garbage: serialise them. */
+int os1_hamming_knn2_noalloc(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t* best_idx, int32_t* best_dist,
+                             int32_t* second_dist, int device, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

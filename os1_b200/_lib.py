@@ -34,6 +34,7 @@ SYMBOLS = [
     ("os1_orb_get_level_keypoints", _i, [_vp, _i, _i, _vp, _i, C.POINTER(_i)]),
     ("os1_descriptor_distance", _i, [_vp, _vp]),
     ("os1_hamming_knn2", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp]),
+    ("os1_hamming_knn2_noalloc", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _vp]),
     ("os1_hamming_window", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
 ]
 

@@ -115,6 +115,9 @@ short sat_short(float v)
 
 } // namespace
 
+// lets the other translation units of the library report through os1_last_error(NULL)
+void os1_internal_set_error(const char* msg) { t_err = msg ? msg : ""; }
+
 // cv::resize INTER_LINEAR taps of one axis: first/second source index (already clamped
 // the way cv::resize clamps them on that axis) and the two 11-bit coefficients.
 void os1_host_resize_taps(int ssize, int dsize, bool vertical, std::vector<short>& s0, std::vector<short>& s1, std::vector<short>& c0,

@@ -13,7 +13,9 @@
 // problem fills the GPU; the per-split partials go through a scratch array and a small merge kernel.
 // window (CSR candidate lists, what Frame::GetFeaturesInArea returns, src/Frame.cc:209-262): one warp per row.
 #include "os1_internal.cuh"
+#include "../../include/os1_b200.h"
 #include <climits>
+#include <mutex>
 
 #define HM_ROWS 128
 #define HM_TILE 256
@@ -137,4 +139,68 @@ cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B
     if (nA <= 0) return cudaSuccess;
     hamming_window_kernel<<<(nA + 3) / 4, 128, 0, s>>>((const uint4*)A, nA, (const uint4*)B, ptr, cand, bestIdx, bestDist, secondDist);
     return cudaGetLastError();
+}
+
+// ---- allocation-free all-pairs matcher --------------------------------------------------------------------------
+// os1_hamming_knn2_noalloc (include/os1_b200.h): same kernels as os1_hamming_knn2, but the per-split partial results
+// live in a fixed array that is part of this library's device image instead of a stream-ordered allocation.
+// Limits: nA <= 4096 rows, nB <= 65536 rows, at most 32 partitions of B -> 32 * 4096 * 8 B = 1 MiB, resident on every
+// GPU that loads the library until the process exits.
+#define OS1_NOALLOC_MAX_A 4096
+#define OS1_NOALLOC_MAX_B 65536
+#define OS1_NOALLOC_MAX_SPLITS 32
+
+static __device__ __align__(256) uint2 g_noalloc_partials[OS1_NOALLOC_MAX_SPLITS * OS1_NOALLOC_MAX_A];
+
+namespace {
+struct NoAllocDevice { uint2* partials; int sms; bool ready; };
+NoAllocDevice g_noalloc_dev[64];
+std::mutex g_noalloc_mu;
+}
+
+void os1_internal_set_error(const char* msg);      // api.cu
+
+extern "C" int os1_hamming_knn2_noalloc(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t* best_idx, int32_t* best_dist,
+                                        int32_t* second_dist, int device, void* cuda_stream)
+{
+    if (nA < 0 || nB < 0 || (nA > 0 && (!A || !best_idx || !best_dist || !second_dist)) || (nB > 0 && !B) || device < 0 || device >= 64) {
+        os1_internal_set_error("os1_hamming_knn2_noalloc: bad argument");
+        return OS1_E_INVALID;
+    }
+    if (nA > OS1_NOALLOC_MAX_A || nB > OS1_NOALLOC_MAX_B) {
+        os1_internal_set_error("os1_hamming_knn2_noalloc: problem larger than the built-in scratch (limits: nA <= 4096, nB <= 65536); "
+                               "use os1_hamming_knn2, which sizes its scratch per call");
+        return OS1_E_CAPACITY;
+    }
+    if (nA == 0) return OS1_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_hamming_knn2_noalloc: cudaSetDevice failed (no CPU fallback)"); return OS1_E_CUDA; }
+    NoAllocDevice dev;
+    {
+        // One-time set-up per device, with that device current: in host code `g_noalloc_partials` is only a handle
+        // for the symbol, not a device address, so the address the kernels need is asked from the runtime.
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        NoAllocDevice& d = g_noalloc_dev[device];
+        if (!d.ready) {
+            uint2* p = nullptr;
+            e = cudaGetSymbolAddress((void**)&p, g_noalloc_partials);
+            if (e != cudaSuccess || !p) {
+                cudaGetLastError();
+                os1_internal_set_error("os1_hamming_knn2_noalloc: cudaGetSymbolAddress(scratch) failed");
+                return OS1_E_CUDA;
+            }
+            int sms = 0;
+            if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms <= 0) { cudaGetLastError(); sms = 148; }
+            d.partials = p; d.sms = sms; d.ready = true;
+        }
+        dev = d;
+    }
+    int nSplit = os1_hamming_splits(nA, nB, dev.sms);
+    if (nSplit > OS1_NOALLOC_MAX_SPLITS) nSplit = OS1_NOALLOC_MAX_SPLITS;
+    // Nothing in the scratch has to start at zero: the merge kernel reads exactly the nSplit x nA partials that the
+    // partial kernel of THIS call has just written; whatever an earlier call left behind is never read.
+    e = os1_launch_hamming_knn2_splits(A, nA, B, nB, best_idx, best_dist, second_dist, (uint64_t*)dev.partials, nSplit,
+                                       (cudaStream_t)cuda_stream);
+    if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_hamming_knn2_noalloc: kernel launch failed"); return OS1_E_CUDA; }
+    return OS1_OK;
 }

@@ -33,6 +33,14 @@ def hamming_knn2_raw(a_ptr, nA, b_ptr, nB, bi_ptr, bd_ptr, sd_ptr, device=0, str
     _lib.check(_lib.load().os1_hamming_knn2(a_ptr, nA, b_ptr, nB, bi_ptr, bd_ptr, sd_ptr, 1, device, stream))
 
 
+def hamming_knn2_noalloc_raw(a_ptr, nA, b_ptr, nB, bi_ptr, bd_ptr, sd_ptr, device=0, stream=None):
+    """os1_hamming_knn2_noalloc: the all-pairs matcher for callers that must not allocate device memory (a frame loop
+    with a deadline, a fully pre-partitioned GPU, a host that forbids allocation on worker threads).  Device pointers
+    only; scratch is a fixed 1 MiB array inside the library, so nA <= 4096 and nB <= 65536, and calls that may overlap
+    on one GPU must be serialised by the caller.  The first call on a device should happen at start-up."""
+    _lib.check(_lib.load().os1_hamming_knn2_noalloc(a_ptr, nA, b_ptr, nB, bi_ptr, bd_ptr, sd_ptr, device, stream))
+
+
 def hamming_window(A, B, ptr, cand, device=0):
     """Best / second best over per-row candidate lists (CSR), e.g. the lists Frame::GetFeaturesInArea returns."""
     A = np.ascontiguousarray(A, np.uint8).reshape(-1, 32)
