@@ -13,7 +13,7 @@
 #define OS1_EDGE 19          // EDGE_THRESHOLD  (ORBextractor.cc:80)
 #define OS1_BORDER 16        // minBorderX = EDGE_THRESHOLD-3 (:807)
 #define OS1_PATH_BITS 12     // quadtree depth representable in a path code (level sides <= 4096 px)
-#define FAST_G 4             // FAST cells per CTA (fast.cu)
+#define FAST_G 8             // FAST cells per CTA (fast.cu)
 
 // packed candidate / kept keypoint: x | y<<12 | score<<24  (x,y relative to (OS1_BORDER,OS1_BORDER))
 #define OS1_PACK_XYS(x, y, s) ((uint32_t)(x) | ((uint32_t)(y) << 12) | ((uint32_t)(s) << 24))
