@@ -6,6 +6,7 @@
 #include <climits>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -49,7 +50,8 @@ struct os1_orb {
     Geometry geom;
     int maxCells = 0;
     int batchCap = 0;
-    PyramidPlan* plan = nullptr;
+    PyramidPlan* plan = nullptr;        // small tiles (single frames)
+    PyramidPlan* planBig = nullptr;     // larger tiles (batches)
     DevBuf rtab, ptab, slab, cellCnt, stage, cand, code, node, candCount, lvKp, lvCount, status, outKp, outDesc, outCount;
     int lastFrames = 0;
     const uint8_t* lastLvl0 = nullptr; long long lastLvl0Stride = 0; int lastLvl0Pitch = 0;
@@ -251,7 +253,23 @@ int build_geometry(os1_orb* h, int rows, int cols)
     CK(cudaMemcpy(h->ptab.p, ptab.data(), ptab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice), "upload path tables");
     if (h->plan) os1_pyramid_plan_destroy(h->plan);
     // coarsest-level tile: small for single frames (more CTAs), the plan is per resolution
-    h->plan = os1_pyramid_plan_create(g, 32, 16);
+    if (h->planBig) os1_pyramid_plan_destroy(h->planBig);
+    h->planBig = nullptr;
+    {
+        // coarsest-level tile: 32x16 keeps a single frame spread over enough CTAs; batches use 48x24 (less halo,
+        // fewer block-wide phases).  A tile whose level-0 footprint exceeds a TMA box (256) falls back to a smaller one.
+        const int cand[][2] = { { 32, 16 }, { 24, 12 }, { 16, 8 }, { 8, 8 } };
+        for (auto& c : cand) {
+            h->plan = os1_pyramid_plan_create(g, c[0], c[1]);
+            if (os1_pyramid_plan_ok(h->plan)) break;
+            os1_pyramid_plan_destroy(h->plan); h->plan = nullptr;
+        }
+        if (!h->plan) return fail(h, OS1_E_UNSUPPORTED, "no pyramid tile fits a TMA box for this scale factor / level count");
+        int tw = 48, th = 24;
+        if (const char* e = getenv("OS1_PYR_TILE")) sscanf(e, "%dx%d", &tw, &th);
+        h->planBig = os1_pyramid_plan_create(g, tw, th);
+        if (!os1_pyramid_plan_ok(h->planBig)) { os1_pyramid_plan_destroy(h->planBig); h->planBig = nullptr; }
+    }
     h->haveGeom = true;
     h->batchCap = 0;
     return OS1_OK;
@@ -323,7 +341,7 @@ int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0
     h->lastFrames = nframes; h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch;
     const bool t = h->timing;
     if (t) CK(cudaEventRecord(h->ev[0], h->stream), "cudaEventRecord");
-    CK(os1_launch_pyramid(h->plan, g, d, nframes, h->stream), "pyramid kernel");
+    CK(os1_launch_pyramid((nframes >= 4 && h->planBig) ? h->planBig : h->plan, g, d, nframes, h->stream), "pyramid kernel");
     if (t) CK(cudaEventRecord(h->ev[1], h->stream), "cudaEventRecord");
     CK(os1_launch_fast(g, d, nframes, h->stream), "FAST kernel");
     if (t) CK(cudaEventRecord(h->ev[2], h->stream), "cudaEventRecord");
@@ -380,6 +398,7 @@ int os1_orb_destroy(os1_orb* h)
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     if (h->plan) os1_pyramid_plan_destroy(h->plan);
+    if (h->planBig) os1_pyramid_plan_destroy(h->planBig);
     DevBuf* bufs[] = { &h->rtab, &h->ptab, &h->slab, &h->cellCnt, &h->stage, &h->cand, &h->code, &h->node, &h->candCount,
                        &h->lvKp, &h->lvCount, &h->status, &h->outKp, &h->outDesc, &h->outCount };
     for (DevBuf* b : bufs) b->release();

@@ -17,9 +17,9 @@
 #define DESC_WARPS 4
 #define WIN 43            // 2*(18+3)+1 : rotated pattern reach 18 (|p| <= 18.38) + blur radius 3
 #define WIN_R 21
-#define RAW_PITCH 48
+#define RAW_PW 13         // window row pitch in words (52 bytes >= 3 + 43, odd)
 #define HB_W 37           // blurred window side
-#define HB_PITCH 38
+#define HB_Q 10           // groups of four blurred columns
 #define BL_PITCH 40
 
 namespace {
@@ -40,9 +40,9 @@ struct DescParams {
 };
 
 struct WarpSmem {
-    uint8_t raw[WIN * RAW_PITCH];
-    uint16_t hb[WIN * HB_PITCH];
-    uint8_t bl[HB_W * BL_PITCH];
+    unsigned raw[WIN * RAW_PW];         // source window as fetched: window column c sits at byte c + shift
+    uint2 hb[WIN * HB_Q];               // horizontal pass, per row and group of four: {(H0,H2), (H1,H3)} as u16x2
+    unsigned bl[HB_W * (BL_PITCH / 4)]; // blurred 37x37 window, bytes
 };
 
 __device__ __forceinline__ int reflect101(int p, int len)
@@ -68,6 +68,12 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x, const DescPara
     if (x < 0) a = __fsub_rn(180.f, a);
     if (y < 0) a = __fsub_rn(360.f, a);
     return a;
+}
+
+// one output of the vertical 7-tap pass: (sum k_j * H_j + 32768) >> 16 with k = {18,34,48,56,48,34,18}
+__device__ __forceinline__ unsigned vtap(int r0, int r1, int r2, int r3, int r4, int r5, int r6)
+{
+    return (unsigned)((18 * (r0 + r6) + 34 * (r1 + r5) + 48 * (r2 + r4) + 56 * r3 + 32768) >> 16);
 }
 
 __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_constant__ DescParams P)
@@ -101,11 +107,28 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     else { img = P.d.slab + (long long)frame * g.slabBytes + L.off; pitch = L.pitch; }
 
     WarpSmem& S = sm[warp];
-    // ---- window -> shared (REFLECT_101 at the level's edges, as the blur of the borderless clone sees it) ----
-    for (int i = lane; i < WIN * WIN; i += 32) {
-        const int r = i / WIN, c = i - r * WIN;
-        const int yy = reflect101(y - WIN_R + r, L.h), xx = reflect101(x - WIN_R + c, L.w);
-        S.raw[r * RAW_PITCH + c] = img[(long long)yy * pitch + xx];
+    // ---- 43x43 window -> shared.  Interior keypoints: aligned 32-bit loads of the rows (12 words cover the 43 bytes
+    // wherever they start); the window keeps the byte phase `sh` of its first column.  Keypoints within 21 px of the
+    // level's edge take the byte path with REFLECT_101 indices, as the blur of the borderless clone sees them. ----------
+    const int xs = x - WIN_R, ys = y - WIN_R;
+    int sh;
+    if (xs >= 0 && ys >= 0 && x + WIN_R < L.w && y + WIN_R < L.h) {
+        sh = xs & 3;
+        const uint8_t* base = img + (long long)ys * pitch + (xs - sh);
+        for (int it = lane; it < WIN * 12; it += 32) {
+            const int r = (it * 5462) >> 16;            // it / 12
+            const int w = it - r * 12;
+            if (4 * w <= sh + WIN - 1)                  // never touch a word that holds no window byte (row end)
+                S.raw[r * RAW_PW + w] = *(const uint32_t*)(base + (long long)r * pitch + 4 * w);
+        }
+    } else {
+        sh = 0;
+        uint8_t* rb = (uint8_t*)S.raw;
+        for (int i = lane; i < WIN * WIN; i += 32) {
+            const int r = i / WIN, c = i - r * WIN;
+            const int yy = reflect101(ys + r, L.h), xx = reflect101(xs + c, L.w);
+            rb[r * (RAW_PW * 4) + c] = img[(long long)yy * pitch + xx];
+        }
     }
     __syncwarp();
 
@@ -115,11 +138,12 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
         const int u = lane - 15;
         if (lane < 31) {
             const int au = u < 0 ? -u : u;
+            const uint8_t* col = (const uint8_t*)S.raw + WIN_R + u + sh;
 #pragma unroll 1
             for (int vv = -15; vv <= 15; vv++) {
                 const int av = vv < 0 ? -vv : vv;
                 if (au <= P.umax[av]) {
-                    const int val = S.raw[(WIN_R + vv) * RAW_PITCH + WIN_R + u];
+                    const int val = col[(WIN_R + vv) * (RAW_PW * 4)];
                     m10 += u * val;
                     m01 += vv * val;
                 }
@@ -134,18 +158,52 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     const float angle = fast_atan2_deg((float)m01, (float)m10, P);
 
     // ---- 7x7 Gaussian, Q8 taps {18,34,48,56,48,34,18}, exact two-pass fixed point ----------------------------------
-    for (int i = lane; i < WIN * HB_W; i += 32) {
-        const int r = i / HB_W, c = i - r * HB_W;
-        const uint8_t* q = S.raw + r * RAW_PITCH + c;       // output column c <-> raw columns c..c+6
-        S.hb[r * HB_PITCH + c] = (uint16_t)(18 * (q[0] + q[6]) + 34 * (q[1] + q[5]) + 48 * (q[2] + q[4]) + 56 * q[3]);
+    // Horizontal pass, four outputs per item on packed u16x2 arithmetic (an output is <= 65280, so two of them share
+    // a 32-bit multiply-add without carries): pair E = outputs (0,2) of the group, pair O = outputs (1,3);
+    // tap i of E is the byte pair (i, i+2) of the aligned 12-byte block, tap i of O is byte pair (i+1, i+3).
+    {
+        const int s8 = 8 * sh;
+        for (int it = lane; it < WIN * HB_Q; it += 32) {
+            const int r = (it * 6554) >> 16;            // it / 10
+            const int q = it - r * HB_Q;
+            const unsigned* w = S.raw + r * RAW_PW + q;
+            const unsigned W0 = w[0], W1 = w[1], W2 = w[2], W3 = w[3];
+            const unsigned A0 = __funnelshift_r(W0, W1, s8), A1 = __funnelshift_r(W1, W2, s8), A2 = __funnelshift_r(W2, W3, s8);
+            const unsigned M = 0x00FF00FFu;
+            const unsigned p0 = A0 & M, p1 = (A0 >> 8) & M, p2 = __funnelshift_r(A0, A1, 16) & M, p3 = __funnelshift_r(A0, A1, 24) & M;
+            const unsigned p4 = A1 & M, p5 = (A1 >> 8) & M, p6 = __funnelshift_r(A1, A2, 16) & M, p7 = __funnelshift_r(A1, A2, 24) & M;
+            uint2 o;
+            o.x = 18u * (p0 + p6) + 34u * (p1 + p5) + 48u * (p2 + p4) + 56u * p3;
+            o.y = 18u * (p1 + p7) + 34u * (p2 + p6) + 48u * (p3 + p5) + 56u * p4;
+            S.hb[r * HB_Q + q] = o;
+        }
     }
     __syncwarp();
-    for (int i = lane; i < HB_W * HB_W; i += 32) {
-        const int r = i / HB_W, c = i - r * HB_W;
-        const uint16_t* q = S.hb + r * HB_PITCH + c;
-        const int s = 18 * (q[0] + q[6 * HB_PITCH]) + 34 * (q[HB_PITCH] + q[5 * HB_PITCH]) + 48 * (q[2 * HB_PITCH] + q[4 * HB_PITCH]) +
-                      56 * q[3 * HB_PITCH];
-        S.bl[r * BL_PITCH + c] = (uint8_t)((s + 32768) >> 16);
+    // Vertical pass: lane = (group of four columns, third of the rows); a 7-row window of unpacked sums slides down.
+    if (lane < 3 * HB_Q) {
+        const int seg = lane / HB_Q, q = lane - seg * HB_Q;
+        const int rb = seg == 0 ? 0 : (seg == 1 ? 13 : 25), re = seg == 0 ? 13 : (seg == 1 ? 25 : 37);
+        int wnd[7][4];                                  // circular: step t keeps rows rb+t .. rb+t+6 in slots (t+j) % 7
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+            const uint2 hh = S.hb[(rb + k) * HB_Q + q];
+            wnd[k][0] = hh.x & 0xFFFF; wnd[k][2] = hh.x >> 16; wnd[k][1] = hh.y & 0xFFFF; wnd[k][3] = hh.y >> 16;
+        }
+#pragma unroll
+        for (int t = 0; t < 13; t++) {
+            const int r = rb + t;
+            if (r < re) {
+                const uint2 hh = S.hb[(r + 6) * HB_Q + q];
+                const int n = (t + 6) % 7;
+                wnd[n][0] = hh.x & 0xFFFF; wnd[n][2] = hh.x >> 16; wnd[n][1] = hh.y & 0xFFFF; wnd[n][3] = hh.y >> 16;
+                unsigned o = 0;
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    o |= vtap(wnd[t % 7][c], wnd[(t + 1) % 7][c], wnd[(t + 2) % 7][c], wnd[(t + 3) % 7][c], wnd[(t + 4) % 7][c],
+                              wnd[(t + 5) % 7][c], wnd[(t + 6) % 7][c]) << (8 * c);
+                S.bl[r * (BL_PITCH / 4) + q] = o;
+            }
+        }
     }
     __syncwarp();
 
@@ -155,7 +213,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     const int4* pat = (const int4*)d_pattern;
     int4 w0 = __ldg(pat + 2 * lane), w1 = __ldg(pat + 2 * lane + 1);
     const int words[8] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w };
-    const uint8_t* center = S.bl + 18 * BL_PITCH + 18;
+    const uint8_t* center = (const uint8_t*)S.bl + 18 * BL_PITCH + 18;
     int val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {

@@ -89,6 +89,7 @@ struct os1_kp_dev { float x, y, size, angle, response; int octave, class_id; };
 struct PyramidPlan;   // host-side tile tables (pyramid.cu)
 PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH);
 void os1_pyramid_plan_destroy(PyramidPlan*);
+bool os1_pyramid_plan_ok(const PyramidPlan*);     // level-0 footprint fits a TMA box and the tile chain fits shared memory
 cudaError_t os1_launch_pyramid(PyramidPlan*, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
 cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
 cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes, int maxQuota, int maxCells, cudaStream_t s);

@@ -28,6 +28,7 @@ struct PyrParams {
     const uint8_t* dbgLvl0; long long dbgStride; int dbgPitch, dbgW, dbgH;
     const int4* xt;              // [level][ntx]  {c0, c1, own0, own1}
     const int4* yt;              // [level][nty]
+    const int4* xg;              // [level][ntx]  thread-mapping constants {ngroups, rcp, nbands, rcp}
     const short4* rtab;          // resize tables {s0, s1, c0, c1}
     uint8_t* slab;
     long long slabBytes;
@@ -72,18 +73,27 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
         : "memory");
 }
 
+// One resized pixel: cv::resize's fixed-point bilinear from the two horizontally
+// interpolated values of the source rows (already >> 4).
+__device__ __forceinline__ unsigned vresize(int h0, int h1, int b0, int b1)
+{
+    return (unsigned)((((b0 * h0) >> 16) + ((b1 * h1) >> 16) + 2) >> 2);
+}
+
 template <bool USE_TMA>
 __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PyrParams p)
 {
     extern __shared__ __align__(128) uint8_t sm_raw[];
     // TMA wants a 128-byte aligned destination: align by hand (the launcher allocates 128 spare bytes) and keep
     // the mbarrier in the same dynamic block
-    uint8_t* sm = (uint8_t*)(((uintptr_t)sm_raw + 127) & ~(uintptr_t)127);
+    // (pointer arithmetic, not an integer round trip, so the compiler keeps addressing it as shared memory)
+    uint8_t* sm = sm_raw + ((128u - ((unsigned)__cvta_generic_to_shared(sm_raw) & 127u)) & 127u);
     uint64_t& bar = *(uint64_t*)(sm + p.barOff);
     const int tx = blockIdx.x, ty = blockIdx.y, frame = blockIdx.z;
     const int tid = threadIdx.y * 32 + threadIdx.x;
 
     int4 PX = p.xt[tx], PY = p.yt[ty];      // level-0 ranges
+    int srcX0 = PX.x, srcY0 = PY.x;         // global coordinates of byte (0,0) of the source level's tile
     if (USE_TMA) {
         if (tid == 0) {
             mbar_init(&bar, 1);
@@ -108,33 +118,76 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
     uint8_t* slab = p.slab + (long long)frame * p.slabBytes;
     for (int l = 1; l < p.nlevels; l++) {
         const int4 X = p.xt[l * p.ntx + tx], Y = p.yt[l * p.nty + ty];
-        const int cw = X.y - X.x, ch = Y.y - Y.x;
+        const int gx0 = X.x & ~3;                                   // tile byte 0 of this level <-> global x = gx0
+        const int ngroups = ((X.y + 3) >> 2) - (gx0 >> 2);           // groups of four destination columns
+        const int rows = Y.y - Y.x;
         const uint8_t* src = sm + p.smemOff[l - 1];
-        uint8_t* dst = sm + p.smemOff[l];
-        const int sp = p.smemPitch[l - 1], dp = p.smemPitch[l];
+        uint32_t* dst = (uint32_t*)(sm + p.smemOff[l]);
+        const int sp = p.smemPitch[l - 1], dpw = p.smemPitch[l] >> 2;
         const short4* rx = p.rtab + p.rxOff[l];
         const short4* ry = p.rtab + p.ryOff[l];
         uint8_t* g = slab + p.lvOff[l];
         const int gp = p.lvPitch[l];
-        for (int lx = threadIdx.x; lx < cw; lx += 32) {
-            const int gx = X.x + lx;
-            const short4 ex = __ldg(rx + gx);
-            const int a0 = ex.x - PX.x, a1 = ex.y - PX.x;
-            const int cx0 = ex.z, cx1 = ex.w;
-            const bool ownx = gx >= X.z && gx < X.w;
-            for (int ly = threadIdx.y; ly < ch; ly += 8) {
-                const int gy = Y.x + ly;
-                const short4 ey = __ldg(ry + gy);
-                const uint8_t* r0 = src + (ey.x - PY.x) * sp;
-                const uint8_t* r1 = src + (ey.y - PY.x) * sp;
-                const int H0 = r0[a0] * cx0 + r0[a1] * cx1;
-                const int H1 = r1[a0] * cx0 + r1[a1] * cx1;
-                const int v = ((((int)ey.z * (H0 >> 4)) >> 16) + (((int)ey.w * (H1 >> 4)) >> 16) + 2) >> 2;
-                dst[ly * dp + lx] = (uint8_t)v;
-                if (ownx && gy >= Y.z && gy < Y.w) g[(long long)gy * gp + gx] = (uint8_t)v;
+        if (ngroups > 0 && rows > 0) {
+            // a thread owns four destination columns and walks a band of rows, so the horizontal taps live in
+            // registers and the horizontally interpolated source row is reused when two destination rows share it
+            // (divisions by per-tile constants through host-made reciprocals: exact for operands < 2^16)
+            const int4 M = p.xg[l * p.ntx + tx];                    // {ngroups, 2^24/ngroups+1, nbands, 2^24/nbands+1}
+            const int nbands = M.z;
+            const int band = (int)(((unsigned)tid * (unsigned)M.y) >> 24), grp = tid - band * ngroups;
+            const int rpb = (int)(((unsigned)(rows + nbands - 1) * (unsigned)M.w) >> 24);
+            const int yb = band * rpb, ye = min(rows, yb + rpb);
+            if (band < nbands && yb < ye) {
+                int a0[4], a1[4], c0[4], c1[4];
+                const int gxb = gx0 + 4 * grp;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int gx = min(max(gxb + i, X.x), X.y - 1);  // columns outside the computed range: results unused
+                    const short4 ex = __ldg(rx + gx);
+                    a0[i] = ex.x - srcX0; a1[i] = ex.y - srcX0; c0[i] = ex.z; c1[i] = ex.w;
+                }
+                const bool fullX = gxb >= X.z && gxb + 4 <= X.w;
+                int h1[4] = { 0, 0, 0, 0 };
+                int prev1 = -1;
+                for (int ly = yb; ly < ye; ly++) {
+                    const int gy = Y.x + ly;
+                    const short4 ey = __ldg(ry + gy);
+                    int h0[4];
+                    if (ey.x == prev1) {
+#pragma unroll
+                        for (int i = 0; i < 4; i++) h0[i] = h1[i];
+                    } else {
+                        const uint8_t* r0 = src + (ey.x - srcY0) * sp;
+#pragma unroll
+                        for (int i = 0; i < 4; i++) h0[i] = (r0[a0[i]] * c0[i] + r0[a1[i]] * c1[i]) >> 4;
+                    }
+                    if (ey.y != ey.x) {
+                        const uint8_t* r1 = src + (ey.y - srcY0) * sp;
+#pragma unroll
+                        for (int i = 0; i < 4; i++) h1[i] = (r1[a0[i]] * c0[i] + r1[a1[i]] * c1[i]) >> 4;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; i++) h1[i] = h0[i];
+                    }
+                    prev1 = ey.y;
+                    const int b0 = ey.z, b1 = ey.w;
+                    const unsigned v0 = vresize(h0[0], h1[0], b0, b1), v1 = vresize(h0[1], h1[1], b0, b1);
+                    const unsigned v2 = vresize(h0[2], h1[2], b0, b1), v3 = vresize(h0[3], h1[3], b0, b1);
+                    const unsigned word = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+                    dst[ly * dpw + grp] = word;
+                    if (gy >= Y.z && gy < Y.w) {
+                        uint8_t* grow = g + (long long)gy * gp + gxb;
+                        if (fullX) *(uint32_t*)grow = word;
+                        else {
+#pragma unroll
+                            for (int i = 0; i < 4; i++)
+                                if (gxb + i >= X.z && gxb + i < X.w) grow[i] = (uint8_t)(word >> (8 * i));
+                        }
+                    }
+                }
             }
         }
-        PX = X; PY = Y;
+        srcX0 = gx0; srcY0 = Y.x;
         __syncthreads();
     }
 }
@@ -145,6 +198,7 @@ struct PyramidPlan {
     int TW, TH, ntx, nty;
     int4* d_xt = nullptr;
     int4* d_yt = nullptr;
+    int4* d_xg = nullptr;
     PyrParams prm;
     int boxW, boxH;
     size_t smemBytes;
@@ -207,17 +261,25 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
     cudaMalloc(&P->d_yt, yt.size() * sizeof(int4));
     cudaMemcpy(P->d_xt, xt.data(), xt.size() * sizeof(int4), cudaMemcpyHostToDevice);
     cudaMemcpy(P->d_yt, yt.data(), yt.size() * sizeof(int4), cudaMemcpyHostToDevice);
+    std::vector<int4> xg(xt.size());
+    for (size_t i = 0; i < xt.size(); i++) {
+        const int ng = std::max(1, ((xt[i].y + 3) >> 2) - ((xt[i].x & ~3) >> 2));
+        const int nb = std::max(1, 256 / ng);
+        xg[i] = make_int4(ng, (1 << 24) / ng + 1, nb, (1 << 24) / nb + 1);
+    }
+    cudaMalloc(&P->d_xg, xg.size() * sizeof(int4));
+    cudaMemcpy(P->d_xg, xg.data(), xg.size() * sizeof(int4), cudaMemcpyHostToDevice);
     PyrParams& p = P->prm;
     memset(&p, 0, sizeof(p));
     p.nlevels = g.nlevels; p.ntx = P->ntx; p.nty = P->nty;
-    p.xt = P->d_xt; p.yt = P->d_yt;
+    p.xt = P->d_xt; p.yt = P->d_yt; p.xg = P->d_xg;
     P->boxW = (mw[0] + 15) & ~15;
     P->boxH = mh[0];
     p.boxBytes = P->boxW * P->boxH;
     size_t off = 0;
     for (int l = 0; l < g.nlevels; l++) {
         p.smemOff[l] = (int)off;
-        p.smemPitch[l] = (l == 0) ? P->boxW : ((mw[l] + 3) & ~3);
+        p.smemPitch[l] = (l == 0) ? P->boxW : ((mw[l] + 3 + 3) & ~3);     // + up to 3 bytes: column 0 sits on a 4-px boundary
         off += (size_t)p.smemPitch[l] * mh[l];
         off = (off + 127) & ~(size_t)127;
         p.rxOff[l] = g.lv[l].rxOff; p.ryOff[l] = g.lv[l].ryOff;
@@ -241,17 +303,22 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
     return P;
 }
 
+bool os1_pyramid_plan_ok(const PyramidPlan* P)
+{
+    return P && P->encode && P->boxW <= 256 && P->boxH <= 256 && P->smemBytes <= 200 * 1024;
+}
+
 void os1_pyramid_plan_destroy(PyramidPlan* P)
 {
     if (!P) return;
-    cudaFree(P->d_xt); cudaFree(P->d_yt);
+    cudaFree(P->d_xt); cudaFree(P->d_yt); cudaFree(P->d_xg);
     delete P;
 }
 
 cudaError_t os1_launch_pyramid(PyramidPlan* P, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s)
 {
     if (g.nlevels < 2) return cudaSuccess;
-    if (!P->encode || P->boxW > 256 || P->boxH > 256 || P->smemBytes > 200 * 1024) return cudaErrorNotSupported;
+    if (!os1_pyramid_plan_ok(P)) return cudaErrorNotSupported;
     CUtensorMap tmap;
     cuuint64_t dims[3] = { (cuuint64_t)g.cols, (cuuint64_t)g.rows, (cuuint64_t)nframes };
     cuuint64_t strides[2] = { (cuuint64_t)d.lvl0Pitch, (cuuint64_t)d.lvl0FrameStride };

@@ -19,7 +19,7 @@
 // Tie rule for equal-size nodes: later-created first (DESIGN.md "canonical tie rule").
 #include "os1_internal.cuh"
 
-#define QT_THREADS 1024
+#define QT_THREADS 512
 #define QT_DONE 0xFFFFu
 #define QT_LEAF 0x80000000u
 
@@ -44,7 +44,7 @@ __device__ __forceinline__ int block_scan_excl(int v, int* warpSums, int& total)
     if (lane == 31) warpSums[w] = inc;
     __syncthreads();
     if (w == 0) {
-        int s = warpSums[lane];
+        int s = lane < QT_THREADS / 32 ? warpSums[lane] : 0;
         int si = s;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -76,7 +76,7 @@ __device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
         }
 }
 
-__global__ void __launch_bounds__(QT_THREADS, 1) quadtree_kernel(const __grid_constant__ QtParams P)
+__global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_constant__ QtParams P)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
     const Geometry& g = P.g;
