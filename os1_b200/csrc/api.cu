@@ -43,6 +43,8 @@ struct os1_orb {
 
     int device;
     cudaStream_t ownStream = nullptr, stream = nullptr;
+    cudaStream_t inStream = nullptr, outStream = nullptr;       // upload / download streams of the chunked host path
+    std::vector<cudaEvent_t> chunkEv;                           // 2 per chunk: uploaded, computed
     std::string err;
 
     // geometry of the current resolution
@@ -327,19 +329,25 @@ int check_status(os1_orb* h, int st)
 }
 
 // the four launches of one extraction over `nframes` frames whose level 0 is already on the device
+// (frames [f0, f0+nframes) of the handle's per-frame buffers; kp/desc/counts are already offset by the caller)
 int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0Pitch, int nframes, os1_kp_dev* kp, uint8_t* desc,
-                 int cap, int* counts)
+                 int cap, int* counts, int f0 = 0)
 {
     const Geometry& g = h->geom;
     DevPtrs d;
-    d.lvl0 = lvl0; d.lvl0FrameStride = lvl0Stride; d.lvl0Pitch = lvl0Pitch;
-    d.slab = (uint8_t*)h->slab.p;
+    const long long F = f0;
+    d.lvl0 = lvl0 + F * lvl0Stride; d.lvl0FrameStride = lvl0Stride; d.lvl0Pitch = lvl0Pitch;
+    d.slab = (uint8_t*)h->slab.p + F * g.slabBytes;
     d.rtab = (const int16_t*)h->rtab.p; d.ptab = (const uint32_t*)h->ptab.p;
-    d.cellCnt = (uint32_t*)h->cellCnt.p; d.stage = (uint32_t*)h->stage.p; d.cand = (uint32_t*)h->cand.p;
-    d.code = (uint32_t*)h->code.p; d.node = (uint16_t*)h->node.p; d.candCount = (uint32_t*)h->candCount.p;
-    d.lvKp = (uint32_t*)h->lvKp.p; d.lvCount = (uint32_t*)h->lvCount.p; d.status = (int*)h->status.p;
-    h->lastFrames = nframes; h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch;
-    const bool t = h->timing;
+    d.cellCnt = (uint32_t*)h->cellCnt.p + F * g.cellsPerFrame;
+    d.stage = (uint32_t*)h->stage.p + F * g.candPerFrame; d.cand = (uint32_t*)h->cand.p + F * g.candPerFrame;
+    d.code = (uint32_t*)h->code.p + F * g.candPerFrame; d.node = (uint16_t*)h->node.p + F * g.candPerFrame;
+    d.candCount = (uint32_t*)h->candCount.p + F * g.nlevels;
+    d.lvKp = (uint32_t*)h->lvKp.p + F * g.kpCapPerFrame; d.lvCount = (uint32_t*)h->lvCount.p + F * g.nlevels;
+    d.status = (int*)h->status.p;
+    if (f0 == 0) { h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch; }
+    h->lastFrames = f0 + nframes;
+    const bool t = h->timing && f0 == 0;
     if (t) CK(cudaEventRecord(h->ev[0], h->stream), "cudaEventRecord");
     CK(os1_launch_pyramid((nframes >= 4 && h->planBig) ? h->planBig : h->plan, g, d, nframes, h->stream), "pyramid kernel");
     if (t) CK(cudaEventRecord(h->ev[1], h->stream), "cudaEventRecord");
@@ -405,6 +413,9 @@ int os1_orb_destroy(os1_orb* h)
     if (h->hostOut) cudaFreeHost(h->hostOut);
     if (h->hostStatus) cudaFreeHost(h->hostStatus);
     for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (cudaEvent_t e : h->chunkEv) cudaEventDestroy(e);
+    if (h->inStream) cudaStreamDestroy(h->inStream);
+    if (h->outStream) cudaStreamDestroy(h->outStream);
     if (h->ownStream) cudaStreamDestroy(h->ownStream);
     delete h;
     return OS1_OK;
@@ -504,70 +515,118 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     const LevelGeom& L0 = g.lv[0];
     uint8_t* slab = (uint8_t*)h->slab.p;
 
-    // ---- level 0 --------------------------------------------------------------------------------------------
-    const uint8_t* lvl0; long long lvl0Stride; int lvl0Pitch;
-    if (frames_on_device && tma_ok(frames, step, frame_stride)) {
-        lvl0 = frames; lvl0Stride = (long long)frame_stride; lvl0Pitch = (int)step;      // read in place
-    } else {
-        // stage into the slab (host frames: this IS the upload; odd device layouts: one D2D copy)
-        cudaMemcpy3DParms p;
-        memset(&p, 0, sizeof(p));
-        p.srcPtr = make_cudaPitchedPtr((void*)frames, step, cols, frame_stride / step);
-        p.dstPtr = make_cudaPitchedPtr(slab + L0.off, L0.pitch, cols, g.slabBytes / L0.pitch);
-        p.extent = make_cudaExtent(cols, rows, nframes);
-        p.kind = frames_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-        if (nframes > 1 && (frame_stride % step != 0 || g.slabBytes % L0.pitch != 0)) {
-            for (int f = 0; f < nframes; f++)
-                CK(cudaMemcpy2DAsync(slab + (long long)f * g.slabBytes + L0.off, L0.pitch, frames + (size_t)f * frame_stride, step, cols, rows,
-                                     p.kind, h->stream), "upload frame");
-        } else if (nframes == 1) {
-            CK(cudaMemcpy2DAsync(slab + L0.off, L0.pitch, frames, step, cols, rows, p.kind, h->stream), "upload frame");
-        } else {
-            CK(cudaMemcpy3DAsync(&p, h->stream), "upload frames");
+    const int cap = g.kpCapPerFrame;
+    const bool direct = frames_on_device && tma_ok(frames, step, frame_stride);      // read level 0 in place
+    const cudaMemcpyKind inKind = frames_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    os1_kp_dev* dKp = out_on_device ? (os1_kp_dev*)kp : (os1_kp_dev*)h->outKp.p;
+    uint8_t* dDesc = out_on_device ? desc : (uint8_t*)h->outDesc.p;
+    int* dCnt = out_on_device ? counts : (int*)h->outCount.p;
+    const int dCap = out_on_device ? cap_per_frame : cap;
+
+    // stage frames [f0, f0+n) into the slab's level 0 (host frames: this IS the upload; odd device layouts: a D2D copy)
+    auto stage_in = [&](int f0, int n, cudaStream_t st) -> cudaError_t {
+        const uint8_t* src = frames + (size_t)f0 * frame_stride;
+        uint8_t* dst = slab + (long long)f0 * g.slabBytes + L0.off;
+        if (n > 1 && frame_stride % step == 0 && g.slabBytes % L0.pitch == 0) {
+            cudaMemcpy3DParms p;
+            memset(&p, 0, sizeof(p));
+            p.srcPtr = make_cudaPitchedPtr((void*)src, step, cols, frame_stride / step);
+            p.dstPtr = make_cudaPitchedPtr(dst, L0.pitch, cols, g.slabBytes / L0.pitch);
+            p.extent = make_cudaExtent(cols, rows, n);
+            p.kind = inKind;
+            return cudaMemcpy3DAsync(&p, st);
         }
-        lvl0 = slab + L0.off; lvl0Stride = g.slabBytes; lvl0Pitch = L0.pitch;
+        for (int f = 0; f < n; f++) {
+            cudaError_t e = cudaMemcpy2DAsync(dst + (long long)f * g.slabBytes, L0.pitch, src + (size_t)f * frame_stride, step, cols, rows, inKind, st);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
+    };
+    const uint8_t* lvl0 = direct ? frames : slab + L0.off;
+    const long long lvl0Stride = direct ? (long long)frame_stride : g.slabBytes;
+    const int lvl0Pitch = direct ? (int)step : L0.pitch;
+
+    // ---- everything on the device: one launch sequence on the handle's stream, nothing to wait for ---------------------
+    if (out_on_device && frames_on_device) {
+        if (!direct) CK(stage_in(0, nframes, h->stream), "stage frames");
+        return run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, nframes, dKp, dDesc, dCap, dCnt);
     }
 
-    // ---- kernels ----------------------------------------------------------------------------------------------
-    if (out_on_device) {
-        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, nframes, (os1_kp_dev*)kp, desc, cap_per_frame, counts);
+    // ---- one frame from the host: the latency path (fetch the count, then only what was produced) -----------------------
+    if (nframes == 1 && !out_on_device) {
+        if (!direct) CK(stage_in(0, 1, h->stream), "upload frame");
+        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, 1, dKp, dDesc, dCap, dCnt);
         if (rc) return rc;
-        if (!frames_on_device) return os1_orb_synchronize(h);      // the host image may be reused by the caller
+        uint8_t* hb = (uint8_t*)h->hostOut;
+        os1_kp_dev* hk = (os1_kp_dev*)hb;
+        uint8_t* hd = hb + (size_t)cap * sizeof(os1_kp_dev);
+        int* hc = (int*)(hd + (size_t)cap * 32);
+        CK(cudaMemcpyAsync(hc, dCnt, 4, cudaMemcpyDeviceToHost, h->stream), "download count");
+        CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
+        CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+        rc = check_status(h, h->hostStatus[0]);
+        if (rc) return rc;
+        const int n = std::min(hc[0], cap);
+        if (n > cap_per_frame) return fail(h, OS1_E_CAPACITY, "os1_orb_extract: caller capacity smaller than the keypoint count (see os1_orb_max_keypoints)");
+        if (n > 0) {
+            CK(cudaMemcpyAsync(hk, dKp, (size_t)n * sizeof(os1_kp_dev), cudaMemcpyDeviceToHost, h->stream), "download keypoints");
+            CK(cudaMemcpyAsync(hd, dDesc, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
+            CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+            memcpy(kp, hk, (size_t)n * sizeof(os1_keypoint));
+            memcpy(desc, hd, (size_t)n * 32);
+        }
+        counts[0] = n;
         return OS1_OK;
     }
-    const int cap = g.kpCapPerFrame;
-    rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, nframes, (os1_kp_dev*)h->outKp.p, (uint8_t*)h->outDesc.p, cap, (int*)h->outCount.p);
-    if (rc) return rc;
-    // ---- results -> pinned mirror -> caller ---------------------------------------------------------------------
-    uint8_t* hb = (uint8_t*)h->hostOut;
-    const size_t kpBytes = (size_t)nframes * cap * sizeof(os1_kp_dev), dBytes = (size_t)nframes * cap * 32;
-    os1_kp_dev* hk = (os1_kp_dev*)hb;
-    uint8_t* hd = hb + kpBytes;
-    int* hc = (int*)(hd + dBytes);
-    CK(cudaMemcpyAsync(hc, h->outCount.p, (size_t)nframes * 4, cudaMemcpyDeviceToHost, h->stream), "download counts");
-    CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
-    if (nframes == 1) {
-        // one frame: wait for the count, then fetch only what was produced
-        CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
-        const int n = std::min(hc[0], cap);
-        if (n > 0) {
-            CK(cudaMemcpyAsync(hk, h->outKp.p, (size_t)n * sizeof(os1_kp_dev), cudaMemcpyDeviceToHost, h->stream), "download keypoints");
-            CK(cudaMemcpyAsync(hd, h->outDesc.p, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
-        }
-    } else {
-        CK(cudaMemcpyAsync(hk, h->outKp.p, kpBytes, cudaMemcpyDeviceToHost, h->stream), "download keypoints");
-        CK(cudaMemcpyAsync(hd, h->outDesc.p, dBytes, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
+
+    // ---- batches with host buffers: chunks flow through upload -> kernels -> download on three streams, so the PCIe
+    // copies of neighbouring chunks hide behind the kernels of the current one ----------------------------------------------
+    int chunk = 32;
+    if (const char* e = getenv("OS1_CHUNK")) chunk = std::max(1, atoi(e));
+    const int nchunks = (nframes + chunk - 1) / chunk;
+    if (!h->inStream) CK(cudaStreamCreateWithFlags(&h->inStream, cudaStreamNonBlocking), "cudaStreamCreate");
+    if (!h->outStream) CK(cudaStreamCreateWithFlags(&h->outStream, cudaStreamNonBlocking), "cudaStreamCreate");
+    while ((int)h->chunkEv.size() < 2 * nchunks + 1) {
+        cudaEvent_t e;
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate");
+        h->chunkEv.push_back(e);
     }
+    // the copy streams must not run ahead of work already queued on the compute stream (buffer reuse across calls)
+    CK(cudaEventRecord(h->chunkEv[2 * nchunks], h->stream), "cudaEventRecord");
+    CK(cudaStreamWaitEvent(h->inStream, h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
+    CK(cudaStreamWaitEvent(h->outStream, h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
+    const size_t kpRow = (size_t)dCap * sizeof(os1_kp_dev), dRow = (size_t)dCap * 32;
+    const int copyCap = std::min(dCap, cap_per_frame);
+    for (int c = 0; c < nchunks; c++) {
+        const int f0 = c * chunk, n = std::min(chunk, nframes - f0);
+        if (!direct) {
+            CK(stage_in(f0, n, frames_on_device ? h->stream : h->inStream), "upload frames");
+            if (!frames_on_device) {
+                CK(cudaEventRecord(h->chunkEv[2 * c], h->inStream), "cudaEventRecord");
+                CK(cudaStreamWaitEvent(h->stream, h->chunkEv[2 * c], 0), "cudaStreamWaitEvent");
+            }
+        }
+        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, n, dKp + (size_t)f0 * dCap, dDesc + (size_t)f0 * dRow, dCap, dCnt + f0, f0);
+        if (rc) return rc;
+        if (!out_on_device) {
+            CK(cudaEventRecord(h->chunkEv[2 * c + 1], h->stream), "cudaEventRecord");
+            CK(cudaStreamWaitEvent(h->outStream, h->chunkEv[2 * c + 1], 0), "cudaStreamWaitEvent");
+            // straight into the caller's slabs (row = frame; pitches differ when the caller's capacity does)
+            CK(cudaMemcpy2DAsync(kp + (size_t)f0 * cap_per_frame, (size_t)cap_per_frame * sizeof(os1_keypoint), dKp + (size_t)f0 * dCap, kpRow,
+                                 (size_t)copyCap * sizeof(os1_keypoint), n, cudaMemcpyDeviceToHost, h->outStream), "download keypoints");
+            CK(cudaMemcpy2DAsync(desc + (size_t)f0 * cap_per_frame * 32, (size_t)cap_per_frame * 32, dDesc + (size_t)f0 * dRow, dRow,
+                                 (size_t)copyCap * 32, n, cudaMemcpyDeviceToHost, h->outStream), "download descriptors");
+            CK(cudaMemcpyAsync(counts + f0, dCnt + f0, (size_t)n * 4, cudaMemcpyDeviceToHost, h->outStream), "download counts");
+        }
+    }
+    CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
     CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    if (!out_on_device) CK(cudaStreamSynchronize(h->outStream), "cudaStreamSynchronize");
     rc = check_status(h, h->hostStatus[0]);
     if (rc) return rc;
-    for (int f = 0; f < nframes; f++) {
-        const int n = hc[f];
-        if (n > cap_per_frame) return fail(h, OS1_E_CAPACITY, "os1_orb_extract: caller capacity smaller than the keypoint count (see os1_orb_max_keypoints)");
-        counts[f] = n;
-        memcpy(kp + (size_t)f * cap_per_frame, hk + (size_t)f * cap, (size_t)n * sizeof(os1_keypoint));
-        memcpy(desc + (size_t)f * cap_per_frame * 32, hd + (size_t)f * cap * 32, (size_t)n * 32);
-    }
+    if (!out_on_device)
+        for (int f = 0; f < nframes; f++)
+            if (counts[f] > cap_per_frame) return fail(h, OS1_E_CAPACITY, "os1_orb_extract_batch: caller capacity smaller than the keypoint count (see os1_orb_max_keypoints)");
     return OS1_OK;
 }
 
