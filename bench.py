@@ -55,7 +55,7 @@ class ClockSampler(threading.Thread):
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             for line in self.proc.stdout:
                 self.rows.append([c.strip() for c in line.split(",")])
                 if self.stop:
@@ -172,11 +172,48 @@ def cpu_baseline_sample():
     reps = 0; t0 = time.perf_counter()
     while True:
         run(); reps += 1
-        if time.perf_counter() - t0 > 10.0 or reps >= 20:
+        if time.perf_counter() - t0 > 12.0 or reps >= 400:
             break
     dt = time.perf_counter() - t0
     return {"value": reps * nframes / dt, "unit": "frames/s", "cores": threads, "kind": kind,
             "sample": "%d x %d synthetic 720p frames, one extractor per thread, %d host threads, %.1f s" % (reps, nframes, threads, dt)}
+
+
+def extras(torch, os1_b200, dev):
+    """Secondary figures of BASELINE.json's metric line: single-frame latency (config 1) and Hamming throughput (config 4)."""
+    from os1_b200 import synth, matcher
+    out = {}
+    # config 1: one 640x480 frame, 1000 features, host buffers in and out (what Frame.cc:133 sees)
+    img = synth.frame(480, 640, 0)
+    e = os1_b200.ORBextractor(1000, 1.2, 8, 20, 7, device=dev.index)
+    for _ in range(20):
+        e(img)
+    ts = []
+    for _ in range(200):
+        t = time.perf_counter(); e(img); ts.append(time.perf_counter() - t)
+    out["latency_ms_640x480_1000feat_host_to_host"] = float(np.median(ts) * 1e3)
+    # config 4: 2000 x 2000 descriptors of two frames extracted with the 2000-feature extractor, all on device
+    fr = synth.video(2, 720, 1280, seed=9)
+    e2 = os1_b200.ORBextractor(2000, 1.2, 8, 20, 7, device=dev.index)
+    d0 = e2(fr[0])[1][:2000]; d1 = e2(fr[1])[1][:2000]
+    a = torch.from_numpy(np.ascontiguousarray(d0)).to(dev); b = torch.from_numpy(np.ascontiguousarray(d1)).to(dev)
+    o = [torch.zeros(len(d0), dtype=torch.int32, device=dev) for _ in range(3)]
+    s = torch.cuda.current_stream(dev)
+    call = lambda: matcher.hamming_knn2_raw(a.data_ptr(), len(d0), b.data_ptr(), len(d1), o[0].data_ptr(), o[1].data_ptr(), o[2].data_ptr(),
+                                            device=dev.index, stream=s.cuda_stream)
+    for _ in range(20):
+        call()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    reps = 200
+    torch.cuda.synchronize(dev); e0.record(s)
+    for _ in range(reps):
+        call()
+    e1.record(s); torch.cuda.synchronize(dev)
+    us = e0.elapsed_time(e1) * 1e3 / reps
+    pairs = len(d0) * len(d1)
+    out["hamming_knn2_%dx%d" % (len(d0), len(d1))] = {"us_per_call": us, "gpairs_per_s": pairs / us / 1e3, "gops_per_s": 24 * pairs / us / 1e3,
+                                                       "note": "1 pair = 8 XOR + 8 POPC + 8 ADD on 32-bit words (SURVEY.md 8d); 2 launches per call"}
+    return out
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -224,10 +261,14 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- device-resident throughput (`value`) + per-kernel durations for the roofline
     ext.set_timing(True)
+    sampler = ClockSampler(local_rank); sampler.start()          # nvidia-smi needs ~0.3 s to come up: start before warm-up
     for _ in range(args.warmup):
         step_device()
     ext.synchronize()
-    sampler = ClockSampler(local_rank); sampler.start()
+    t_wait = time.time()
+    while len(sampler.rows) < 2 and time.time() - t_wait < 3.0:    # keep the GPU busy until the sampler is reporting
+        step_device(); ext.synchronize()
+    sampler.rows = []
     barrier()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     stage_ms = np.zeros(4)
@@ -259,6 +300,37 @@ def run_ours(args, rank, world, local_rank):
     assert np.array_equal(cnt_h.numpy(), counts), "host and device paths disagree on keypoint counts"
     nkp = int(counts.sum())
 
+    # ---- the path's one exchange step (N > 1): all-gather descriptor slabs over NCCL, then each rank matches its
+    # share of the cross-frame pairs (BASELINE.json configs[4], scaled to the first frames of every rank)
+    sweep = None
+    if dist is not None:
+        from os1_b200 import shard
+        Fl = min(8, B)
+        dsl = desc_d[:Fl].contiguous(); csl = cnt_d[:Fl].contiguous()
+        shard.allgather_descriptors(dsl, csl)             # warm-up (NCCL channel set-up)
+        barrier()
+        s0 = torch.cuda.Event(enable_timing=True); s1 = torch.cuda.Event(enable_timing=True); s2 = torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        d_all, c_all = shard.allgather_descriptors(dsl, csl)
+        s1.record(stream)
+        pairs = shard.pair_partition(Fl * world, rank, world)
+        acc = shard.sweep_pairs(d_all, c_all, pairs, local_rank)
+        s2.record(stream)
+        barrier()
+        tg = torch.tensor([s0.elapsed_time(s1), s1.elapsed_time(s2), float(len(pairs)), float(acc.sum())], device=dev, dtype=torch.float64)
+        tmax = tg.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = tg.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        npairs = int(tsum[2].item())
+        cmean = float(c_all.float().mean().item())
+        sweep = {"frames": Fl * world, "frame_pairs": npairs, "allgather_ms": float(tmax[0].item()),
+                 "allgather_bytes_per_rank": int(dsl.numel() + csl.numel() * 4),
+                 "match_ms": float(tmax[1].item()), "accepted_matches": int(tsum[3].item()),
+                 "gpairs_per_s": npairs * cmean * cmean / (float(tmax[1].item()) * 1e-3) / 1e9,
+                 "note": "descriptor pairs/s over all ranks incl. per-pair launch + acceptance test; NCCL all_gather_into_tensor"}
+
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
     if rank != 0:
         return
     fps = world * B * args.steps / (ms * 1e-3)
@@ -288,7 +360,13 @@ def run_ours(args, rank, world, local_rank):
                     "d2h_bytes_per_step": int(B * cap * 60 + B * 4 + 4)},
             "gpu_launches": int(args.steps * ext.launches_per_call()),
             "roofline": roof, "clocks": clocks}
+    if sweep is not None:
+        line["sweep"] = sweep
     if world == 1:
+        try:
+            line["extras"] = extras(torch, os1_b200, dev)
+        except Exception as ex:
+            line["extras"] = {"error": str(ex)}
         try:
             line["cpu_baseline"] = cpu_baseline_sample()
         except Exception as ex:           # the checker libraries are optional on the box; say so rather than fail the bench
@@ -299,7 +377,7 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=256, help="frames per step per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
