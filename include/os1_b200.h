@@ -117,6 +117,33 @@ int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t
 int os1_hamming_window(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, int32_t* best_idx,
                        int32_t* best_dist, int32_t* second_dist, int on_device, int device, void* cuda_stream);
 
+/* Distance of every entry of the candidate lists: dist[k] = DescriptorDistance(A[i], B[cand[k]]) for ptr[i] <= k < ptr[i+1]
+ * (src/ORBmatcher.cc:1605-1621 evaluated for the whole of a matcher's scan in one launch). */
+int os1_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, uint16_t* dist,
+                    int on_device, int device, void* cuda_stream);
+
+/* The matching loops of the three consumers named in BASELINE.json, with their in-order bookkeeping.  HOST buffers.
+ * Candidate lists are what Frame::GetFeaturesInArea returns per query (src/Frame.cc:209-262), concatenated CSR-style
+ * in the reference's visiting order; a query the reference skips (`continue`) simply has an empty list.  All
+ * distances are computed on the GPU in one launch; the ordered accept / claim pass runs on the host over them.
+ *
+ * ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:400-515: ratio test with TH_LOW = 50, partners already
+ * claimed with a smaller-or-equal distance are skipped (:439), a better later match steals the partner (:458-466),
+ * rotation-histogram filter when both angle arrays are given (:468-505).  matches12[i1] = index in D2 or -1. */
+int os1_search_for_initialization(const uint8_t* D1, int n1, const uint8_t* D2, int n2, const int32_t* ptr, const int32_t* cand,
+                                  float nnratio, const float* angles1, const float* angles2, int32_t* matches12, int* nmatches, int device);
+/* ORBmatcher::SearchByProjection(Frame&, const Frame&, th), src/ORBmatcher.cc:1292-1423 from the candidate lists on
+ * (:1349): best only, accept <= TH_HIGH = 100 (:1379); taken[i2] != 0 <=> CurrentFrame.mvpMapPoints[i2] already holds
+ * an observed point (:1363-1365) and is updated as matches are made (:1381); rotation filter when angles are given.
+ * match_of_cand[i2] = query index or -1. */
+int os1_search_by_projection_frame(const uint8_t* Dq, int nq, const uint8_t* Dc, int nc, const int32_t* ptr, const int32_t* cand,
+                                   uint8_t* taken, const float* angles_q, const float* angles_c, int32_t* match_of_cand, int* nmatches, int device);
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th), src/ORBmatcher.cc:45-124 from the candidate
+ * lists on (:73): best and second best with the ratio applied only when both lie in the same pyramid level
+ * (:113-114; octave_c = octave of every frame keypoint), accept <= TH_HIGH. */
+int os1_search_by_projection_points(const uint8_t* Dq, int nq, const uint8_t* Dc, int nc, const int32_t* ptr, const int32_t* cand,
+                                    uint8_t* taken, const int32_t* octave_c, float nnratio, int32_t* match_of_cand, int* nmatches, int device);
+
 /* os1_hamming_knn2 for callers that must not allocate.  This entry point has no counterpart in the reference
  * (os1 has no GPU code and so no allocation policy to mirror); it exists for the hosts this library gets embedded in.
  *

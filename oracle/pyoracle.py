@@ -68,6 +68,8 @@ class Oracle:
             L.orc_hamming_knn2_mt.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _i]
             L.orc_hamming_window.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
             L.orc_search_for_initialization.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp]
+            L.orc_search_by_projection_frame.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
+            L.orc_search_by_projection_points.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp]
             cls._lib = L
         return cls._lib
 
@@ -188,6 +190,27 @@ class Oracle:
         n = cls.lib().orc_search_for_initialization(_p(D1), len(D1), _p(D2), len(D2), _p(ptr), _p(cand), nnratio,
                                                      None if a1 is None else _p(a1), None if a2 is None else _p(a2), _p(m))
         return n, m
+
+    @classmethod
+    def search_by_projection_frame(cls, Dq, Dc, ptr, cand, taken, angles_q=None, angles_c=None):
+        Dq = np.ascontiguousarray(Dq, np.uint8); Dc = np.ascontiguousarray(Dc, np.uint8)
+        ptr = np.ascontiguousarray(ptr, np.int32); cand = np.ascontiguousarray(cand, np.int32)
+        aq = None if angles_q is None else np.ascontiguousarray(angles_q, np.float32)
+        ac = None if angles_c is None else np.ascontiguousarray(angles_c, np.float32)
+        m = np.zeros(max(len(Dc), 1), np.int32)
+        n = cls.lib().orc_search_by_projection_frame(_p(Dq), len(Dq), _p(Dc), len(Dc), _p(ptr), _p(cand), _p(taken),
+                                                     None if aq is None else _p(aq), None if ac is None else _p(ac), _p(m))
+        return n, m[:len(Dc)]
+
+    @classmethod
+    def search_by_projection_points(cls, Dq, Dc, ptr, cand, taken, octave_c, nnratio=0.8):
+        Dq = np.ascontiguousarray(Dq, np.uint8); Dc = np.ascontiguousarray(Dc, np.uint8)
+        ptr = np.ascontiguousarray(ptr, np.int32); cand = np.ascontiguousarray(cand, np.int32)
+        octave_c = np.ascontiguousarray(octave_c, np.int32)
+        m = np.zeros(max(len(Dc), 1), np.int32)
+        n = cls.lib().orc_search_by_projection_points(_p(Dq), len(Dq), _p(Dc), len(Dc), _p(ptr), _p(cand), _p(taken), _p(octave_c),
+                                                      nnratio, _p(m))
+        return n, m[:len(Dc)]
 
     @classmethod
     def extract_batch(cls, frames, params, threads):

@@ -106,7 +106,28 @@ __global__ void __launch_bounds__(128) hamming_window_kernel(const uint4* __rest
     }
 }
 
+// dist[k] = distance(A[row of k], B[cand[k]]) for every CSR entry; one warp per row
+__global__ void __launch_bounds__(128) hamming_csr_kernel(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B,
+                                                          const int* __restrict__ ptr, const int* __restrict__ cand, uint16_t* __restrict__ dist)
+{
+    const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= nA) return;
+    const uint4 a0 = __ldg(A + 2 * row), a1 = __ldg(A + 2 * row + 1);
+    const int p0 = ptr[row], p1 = ptr[row + 1];
+    for (int k = p0 + lane; k < p1; k += 32) {
+        const int j = __ldg(cand + k);
+        dist[k] = (uint16_t)dist256(a0, a1, __ldg(B + 2 * (long long)j), __ldg(B + 2 * (long long)j + 1));
+    }
+}
+
 } // namespace
+
+cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s)
+{
+    if (nA <= 0) return cudaSuccess;
+    hamming_csr_kernel<<<(nA + 3) / 4, 128, 0, s>>>((const uint4*)A, nA, (const uint4*)B, ptr, cand, dist);
+    return cudaGetLastError();
+}
 
 // number of B partitions used for an nA x nB problem on a GPU with `sms` SMs
 int os1_hamming_splits(int nA, int nB, int sms)

@@ -101,3 +101,5 @@ cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8
                                            int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s);
 cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, int* bestIdx,
                                       int* bestDist, int* secondDist, cudaStream_t s);
+cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s);
+void os1_internal_set_error(const char* msg);

@@ -52,3 +52,57 @@ def hamming_window(A, B, ptr, cand, device=0):
     _lib.check(_lib.load().os1_hamming_window(_ptr(A), len(A), _ptr(B), len(B), _ptr(ptr), _ptr(cand), _ptr(bi), _ptr(bd),
                                               _ptr(sd), 0, device, None))
     return bi, bd, sd
+
+
+def _csr(ptr, cand):
+    return np.ascontiguousarray(ptr, np.int32), np.ascontiguousarray(cand, np.int32)
+
+
+def hamming_csr(A, B, ptr, cand, device=0):
+    """Distance of every candidate-list entry (uint16)."""
+    A = np.ascontiguousarray(A, np.uint8).reshape(-1, 32); B = np.ascontiguousarray(B, np.uint8).reshape(-1, 32)
+    ptr, cand = _csr(ptr, cand)
+    dist = np.zeros(max(len(cand), 1), np.uint16)
+    _lib.check(_lib.load().os1_hamming_csr(_ptr(A), len(A), _ptr(B), len(B), _ptr(ptr), _ptr(cand), _ptr(dist), 0, device, None))
+    return dist[:len(cand)]
+
+
+def SearchForInitialization(D1, D2, ptr, cand, nnratio=0.9, angles1=None, angles2=None, device=0):
+    """Matching loop of ORBmatcher::SearchForInitialization (ORBmatcher.cc:400-515) over CSR candidate lists.
+    Returns (nmatches, vnMatches12)."""
+    D1 = np.ascontiguousarray(D1, np.uint8).reshape(-1, 32); D2 = np.ascontiguousarray(D2, np.uint8).reshape(-1, 32)
+    ptr, cand = _csr(ptr, cand)
+    a1 = None if angles1 is None else np.ascontiguousarray(angles1, np.float32)
+    a2 = None if angles2 is None else np.ascontiguousarray(angles2, np.float32)
+    m = np.zeros(max(len(D1), 1), np.int32); n = C.c_int()
+    _lib.check(_lib.load().os1_search_for_initialization(_ptr(D1), len(D1), _ptr(D2), len(D2), _ptr(ptr), _ptr(cand), nnratio,
+                                                          None if a1 is None else _ptr(a1), None if a2 is None else _ptr(a2), _ptr(m),
+                                                          C.byref(n), device))
+    return n.value, m[:len(D1)]
+
+
+def SearchByProjectionFrame(Dq, Dc, ptr, cand, taken, angles_q=None, angles_c=None, device=0):
+    """Matching loop of ORBmatcher::SearchByProjection(Frame&, const Frame&, th) (ORBmatcher.cc:1349-1419).
+    `taken` (uint8 per current-frame keypoint) is updated in place.  Returns (nmatches, match_of_cand)."""
+    Dq = np.ascontiguousarray(Dq, np.uint8).reshape(-1, 32); Dc = np.ascontiguousarray(Dc, np.uint8).reshape(-1, 32)
+    ptr, cand = _csr(ptr, cand)
+    assert taken.dtype == np.uint8 and taken.flags.c_contiguous and len(taken) == len(Dc)
+    aq = None if angles_q is None else np.ascontiguousarray(angles_q, np.float32)
+    ac = None if angles_c is None else np.ascontiguousarray(angles_c, np.float32)
+    m = np.zeros(max(len(Dc), 1), np.int32); n = C.c_int()
+    _lib.check(_lib.load().os1_search_by_projection_frame(_ptr(Dq), len(Dq), _ptr(Dc), len(Dc), _ptr(ptr), _ptr(cand), _ptr(taken),
+                                                           None if aq is None else _ptr(aq), None if ac is None else _ptr(ac), _ptr(m),
+                                                           C.byref(n), device))
+    return n.value, m[:len(Dc)]
+
+
+def SearchByProjectionPoints(Dq, Dc, ptr, cand, taken, octave_c, nnratio=0.8, device=0):
+    """Matching loop of ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (ORBmatcher.cc:73-121)."""
+    Dq = np.ascontiguousarray(Dq, np.uint8).reshape(-1, 32); Dc = np.ascontiguousarray(Dc, np.uint8).reshape(-1, 32)
+    ptr, cand = _csr(ptr, cand)
+    octave_c = np.ascontiguousarray(octave_c, np.int32)
+    assert taken.dtype == np.uint8 and taken.flags.c_contiguous and len(taken) == len(Dc)
+    m = np.zeros(max(len(Dc), 1), np.int32); n = C.c_int()
+    _lib.check(_lib.load().os1_search_by_projection_points(_ptr(Dq), len(Dq), _ptr(Dc), len(Dc), _ptr(ptr), _ptr(cand), _ptr(taken),
+                                                            _ptr(octave_c), nnratio, _ptr(m), C.byref(n), device))
+    return n.value, m[:len(Dc)]
