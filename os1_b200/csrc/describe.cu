@@ -40,9 +40,9 @@ struct DescParams {
 };
 
 struct WarpSmem {
-    unsigned raw[WIN * RAW_PW];         // source window as fetched: window column c sits at byte c + shift
+    unsigned raw[WIN * RAW_PW];         // source window as fetched: window column c sits at byte c + shift;
+                                        // after the horizontal pass the same words hold the blurred 37x37 window (bytes)
     uint2 hb[WIN * HB_Q];               // horizontal pass, per row and group of four: {(H0,H2), (H1,H3)} as u16x2
-    unsigned bl[HB_W * (BL_PITCH / 4)]; // blurred 37x37 window, bytes
 };
 
 __device__ __forceinline__ int reflect101(int p, int len)
@@ -76,7 +76,7 @@ __device__ __forceinline__ unsigned vtap(int r0, int r1, int r2, int r3, int r4,
     return (unsigned)((18 * (r0 + r6) + 34 * (r1 + r5) + 48 * (r2 + r4) + 56 * r3 + 32768) >> 16);
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_constant__ DescParams P)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __grid_constant__ DescParams P)
 {
     __shared__ WarpSmem sm[DESC_WARPS];
     const Geometry& g = P.g;
@@ -119,8 +119,10 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
             const int r = (it * 5462) >> 16;            // it / 12
             const int w = it - r * 12;
             if (4 * w <= sh + WIN - 1)                  // never touch a word that holds no window byte (row end)
-                S.raw[r * RAW_PW + w] = *(const uint32_t*)(base + (long long)r * pitch + 4 * w);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(S.raw + r * RAW_PW + w)),
+                             "l"(base + (long long)r * pitch + 4 * w) : "memory");      // all 17 copies of a lane in flight at once
         }
+        asm volatile("cp.async.wait_all;" ::: "memory");
     } else {
         sh = 0;
         uint8_t* rb = (uint8_t*)S.raw;
@@ -179,6 +181,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
         }
     }
     __syncwarp();
+    unsigned* bl = S.raw;               // the raw window is dead from here on (37 * 10 words <= 43 * 13)
     // Vertical pass: lane = (group of four columns, third of the rows); a 7-row window of unpacked sums slides down.
     if (lane < 3 * HB_Q) {
         const int seg = lane / HB_Q, q = lane - seg * HB_Q;
@@ -201,7 +204,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
                 for (int c = 0; c < 4; c++)
                     o |= vtap(wnd[t % 7][c], wnd[(t + 1) % 7][c], wnd[(t + 2) % 7][c], wnd[(t + 3) % 7][c], wnd[(t + 4) % 7][c],
                               wnd[(t + 5) % 7][c], wnd[(t + 6) % 7][c]) << (8 * c);
-                S.bl[r * (BL_PITCH / 4) + q] = o;
+                bl[r * (BL_PITCH / 4) + q] = o;
             }
         }
     }
@@ -213,7 +216,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) describe_kernel(const __grid_
     const int4* pat = (const int4*)d_pattern;
     int4 w0 = __ldg(pat + 2 * lane), w1 = __ldg(pat + 2 * lane + 1);
     const int words[8] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w };
-    const uint8_t* center = (const uint8_t*)S.bl + 18 * BL_PITCH + 18;
+    const uint8_t* center = (const uint8_t*)bl + 18 * BL_PITCH + 18;
     int val = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
