@@ -29,6 +29,8 @@ struct PyrParams {
     const int4* xt;              // [level][ntx]  {c0, c1, own0, own1}
     const int4* yt;              // [level][nty]
     const int4* xg;              // [level][ntx]  thread-mapping constants {ngroups, rcp, nbands, rcp}
+    const int4* qtab;            // per level, per group of four destination columns: 2 x int4 (see QuadTaps)
+    int qOff[OS1_MAX_LEVELS];    // first entry (in int4 units) of a level in qtab
     const short4* rtab;          // resize tables {s0, s1, c0, c1}
     uint8_t* slab;
     long long slabBytes;
@@ -124,7 +126,6 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
         const uint8_t* src = sm + p.smemOff[l - 1];
         uint32_t* dst = (uint32_t*)(sm + p.smemOff[l]);
         const int sp = p.smemPitch[l - 1], dpw = p.smemPitch[l] >> 2;
-        const short4* rx = p.rtab + p.rxOff[l];
         const short4* ry = p.rtab + p.ryOff[l];
         uint8_t* g = slab + p.lvOff[l];
         const int gp = p.lvPitch[l];
@@ -138,42 +139,55 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
             const int rpb = (int)(((unsigned)(rows + nbands - 1) * (unsigned)M.w) >> 24);
             const int yb = band * rpb, ye = min(rows, yb + rpb);
             if (band < nbands && yb < ye) {
-                int a0[4], a1[4], c0[4], c1[4];
+                // horizontal taps of the four columns, prepared on the host (QuadTaps): three consecutive source words
+                // hold all eight taps; two byte-permutes line them up as (p0,p1) byte pairs and one dp2a per pixel does
+                // p0*c0 + p1*c1
+                const int gq = (gx0 >> 2) + grp;                 // global group index
+                const int4 t0 = __ldg(p.qtab + p.qOff[l] + 2 * gq), t1 = __ldg(p.qtab + p.qOff[l] + 2 * gq + 1);
+                // first source word, relative to the tile (columns left of the computed range may point before it:
+                // their results are discarded, so any in-bounds word will do)
+                const int wb = max(t0.x - (srcX0 >> 2), 0);
+                const unsigned selLo01 = (unsigned)t0.y & 0xFFFFu, selHi01 = (unsigned)t0.y >> 16;
+                const unsigned selLo23 = (unsigned)t0.z & 0xFFFFu, selHi23 = (unsigned)t0.z >> 16;
+                const unsigned A0 = t1.x, A1 = t1.y, A2 = t1.z, A3 = t1.w;       // c0 | c1 << 16 per column
                 const int gxb = gx0 + 4 * grp;
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int gx = min(max(gxb + i, X.x), X.y - 1);  // columns outside the computed range: results unused
-                    const short4 ex = __ldg(rx + gx);
-                    a0[i] = ex.x - srcX0; a1[i] = ex.y - srcX0; c0[i] = ex.z; c1[i] = ex.w;
-                }
                 const bool fullX = gxb >= X.z && gxb + 4 <= X.w;
-                int h1[4] = { 0, 0, 0, 0 };
+                const uint32_t* src32 = (const uint32_t*)src;
+                const int spw = sp >> 2;
+                auto hrow = [&](int srow, unsigned (&h)[4]) {
+                    const uint32_t* r = src32 + (srow - srcY0) * spw + wb;
+                    const unsigned w0 = r[0], w1 = r[1], w2 = r[2];
+                    const unsigned B01 = __byte_perm(__byte_perm(w0, w1, selLo01), w2, selHi01);
+                    const unsigned B23 = __byte_perm(__byte_perm(w0, w1, selLo23), w2, selHi23);
+                    // kept as ((H >> 4) << 16): the vertical pass then needs one multiply-high per tap
+                    h[0] = (__dp2a_lo(A0, B01, 0u) << 12) & 0xFFFF0000u;
+                    h[1] = (__dp2a_hi(A1, B01, 0u) << 12) & 0xFFFF0000u;
+                    h[2] = (__dp2a_lo(A2, B23, 0u) << 12) & 0xFFFF0000u;
+                    h[3] = (__dp2a_hi(A3, B23, 0u) << 12) & 0xFFFF0000u;
+                };
+                unsigned h0[4], h1[4] = { 0, 0, 0, 0 };
                 int prev1 = -1;
                 for (int ly = yb; ly < ye; ly++) {
                     const int gy = Y.x + ly;
                     const short4 ey = __ldg(ry + gy);
-                    int h0[4];
                     if (ey.x == prev1) {
 #pragma unroll
                         for (int i = 0; i < 4; i++) h0[i] = h1[i];
-                    } else {
-                        const uint8_t* r0 = src + (ey.x - srcY0) * sp;
-#pragma unroll
-                        for (int i = 0; i < 4; i++) h0[i] = (r0[a0[i]] * c0[i] + r0[a1[i]] * c1[i]) >> 4;
-                    }
-                    if (ey.y != ey.x) {
-                        const uint8_t* r1 = src + (ey.y - srcY0) * sp;
-#pragma unroll
-                        for (int i = 0; i < 4; i++) h1[i] = (r1[a0[i]] * c0[i] + r1[a1[i]] * c1[i]) >> 4;
-                    } else {
+                    } else hrow(ey.x, h0);
+                    if (ey.y != ey.x) hrow(ey.y, h1);
+                    else {
 #pragma unroll
                         for (int i = 0; i < 4; i++) h1[i] = h0[i];
                     }
                     prev1 = ey.y;
-                    const int b0 = ey.z, b1 = ey.w;
-                    const unsigned v0 = vresize(h0[0], h1[0], b0, b1), v1 = vresize(h0[1], h1[1], b0, b1);
-                    const unsigned v2 = vresize(h0[2], h1[2], b0, b1), v3 = vresize(h0[3], h1[3], b0, b1);
-                    const unsigned word = v0 | (v1 << 8) | (v2 << 16) | (v3 << 24);
+                    const unsigned b0 = (unsigned)ey.z, b1 = (unsigned)ey.w;
+                    unsigned word = 0;
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        // ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2, each product taken as a multiply-high
+                        const unsigned v = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
+                        word |= v << (8 * i);
+                    }
                     dst[ly * dpw + grp] = word;
                     if (gy >= Y.z && gy < Y.w) {
                         uint8_t* grow = g + (long long)gy * gp + gxb;
@@ -199,6 +213,8 @@ struct PyramidPlan {
     int4* d_xt = nullptr;
     int4* d_yt = nullptr;
     int4* d_xg = nullptr;
+    int4* d_qtab = nullptr;
+    bool tapsFit = true;       // every group of four columns finds its eight taps in three consecutive source words
     PyrParams prm;
     int boxW, boxH;
     size_t smemBytes;
@@ -241,7 +257,9 @@ static void build_axis(const Geometry& g, bool vertical, int T, int& nt, std::ve
             if (l == 0) break;
             int n0 = b[l - 1][t], n1 = b[l - 1][t + 1];
             if (c1 > c0) {
-                n0 = std::min(n0, (int)S0[l][c0]);
+                // (x axis: threads work on groups of four columns, and a group's source words are anchored at its
+                //  FIRST column's tap, so the footprint starts at the tap of the group that contains c0)
+                n0 = std::min(n0, (int)S0[l][vertical ? c0 : (c0 & ~3)]);
                 n1 = std::max(n1, (int)S1[l][c1 - 1] + 1);
             }
             c0 = n0; c1 = n1;
@@ -273,6 +291,42 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
     memset(&p, 0, sizeof(p));
     p.nlevels = g.nlevels; p.ntx = P->ntx; p.nty = P->nty;
     p.xt = P->d_xt; p.yt = P->d_yt; p.xg = P->d_xg;
+    {
+        // QuadTaps: for destination columns 4q..4q+3 of level l — int4 #0 = {first source word (global index),
+        // selLo01 | selHi01 << 16, selLo23 | selHi23 << 16, 0}, int4 #1 = {c0 | c1 << 16 for the four columns}.
+        // Tap byte o (0..11, relative to the first word) is routed by two byte-permutes: the first picks from words
+        // 0-1, the second substitutes bytes that live in word 2.
+        std::vector<int4> q;
+        for (int l = 1; l < g.nlevels; l++) {
+            p.qOff[l] = (int)q.size();
+            std::vector<short> s0, s1, c0, c1;
+            os1_host_resize_taps(g.lv[l - 1].w, g.lv[l].w, false, s0, s1, c0, c1);
+            const int W = g.lv[l].w, nq = (W + 3) / 4;
+            for (int qi = 0; qi < nq; qi++) {
+                int a[8]; unsigned A[4];
+                for (int i = 0; i < 4; i++) {
+                    const int x = std::min(4 * qi + i, W - 1);
+                    a[2 * i] = s0[x]; a[2 * i + 1] = s1[x];
+                    A[i] = (unsigned)(unsigned short)c0[x] | ((unsigned)(unsigned short)c1[x] << 16);
+                }
+                const int wbase = a[0] >> 2;
+                unsigned sel[2][2] = { { 0, 0 }, { 0, 0 } };
+                for (int k = 0; k < 8; k++) {
+                    const int o = a[k] - 4 * wbase;
+                    if (o < 0 || o > 11) { P->tapsFit = false; continue; }
+                    const int word = k >> 2, byte = k & 3;
+                    sel[word][0] |= (unsigned)(o < 8 ? o : 0) << (4 * byte);
+                    sel[word][1] |= (unsigned)(o < 8 ? byte : 4 + (o - 8)) << (4 * byte);
+                }
+                q.push_back(make_int4(wbase, (int)(sel[0][0] | (sel[0][1] << 16)), (int)(sel[1][0] | (sel[1][1] << 16)), 0));
+                q.push_back(make_int4((int)A[0], (int)A[1], (int)A[2], (int)A[3]));
+            }
+        }
+        if (q.empty()) q.push_back(make_int4(0, 0, 0, 0));
+        cudaMalloc(&P->d_qtab, q.size() * sizeof(int4));
+        cudaMemcpy(P->d_qtab, q.data(), q.size() * sizeof(int4), cudaMemcpyHostToDevice);
+        p.qtab = P->d_qtab;
+    }
     P->boxW = (mw[0] + 15) & ~15;
     P->boxH = mh[0];
     p.boxBytes = P->boxW * P->boxH;
@@ -305,13 +359,13 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
 
 bool os1_pyramid_plan_ok(const PyramidPlan* P)
 {
-    return P && P->encode && P->boxW <= 256 && P->boxH <= 256 && P->smemBytes <= 200 * 1024;
+    return P && P->encode && P->tapsFit && P->boxW <= 256 && P->boxH <= 256 && P->smemBytes <= 200 * 1024;
 }
 
 void os1_pyramid_plan_destroy(PyramidPlan* P)
 {
     if (!P) return;
-    cudaFree(P->d_xt); cudaFree(P->d_yt); cudaFree(P->d_xg);
+    cudaFree(P->d_xt); cudaFree(P->d_yt); cudaFree(P->d_xg); cudaFree(P->d_qtab);
     delete P;
 }
 
