@@ -213,6 +213,32 @@ def extras(torch, os1_b200, dev):
     pairs = len(d0) * len(d1)
     out["hamming_knn2_%dx%d" % (len(d0), len(d1))] = {"us_per_call": us, "gpairs_per_s": pairs / us / 1e3, "gops_per_s": 24 * pairs / us / 1e3,
                                                        "note": "1 pair = 8 XOR + 8 POPC + 8 ADD on 32-bit words (SURVEY.md 8d); 2 launches per call"}
+    call2 = lambda: matcher.hamming_knn2_noalloc_raw(a.data_ptr(), len(d0), b.data_ptr(), len(d1), o[0].data_ptr(), o[1].data_ptr(),
+                                                     o[2].data_ptr(), device=dev.index, stream=s.cuda_stream)
+    for _ in range(20):
+        call2()
+    torch.cuda.synchronize(dev); e0.record(s)
+    for _ in range(reps):
+        call2()
+    e1.record(s); torch.cuda.synchronize(dev)
+    us2 = e0.elapsed_time(e1) * 1e3 / reps
+    out["hamming_knn2_noalloc_%dx%d" % (len(d0), len(d1))] = {"us_per_call": us2, "gpairs_per_s": pairs / us2 / 1e3, "gops_per_s": 24 * pairs / us2 / 1e3}
+    # cross-frame sweep on one GPU: all pairs of 48 frames of a video, one launch
+    from os1_b200 import shard
+    F = 48
+    vid = synth.video(F, 720, 1280, seed=77)
+    e3 = os1_b200.ORBextractor(1500, 1.2, 8, 20, 7, device=dev.index)
+    kp_, desc_, cnt_ = e3.extract_batch(vid)
+    dsl = torch.from_numpy(desc_).to(dev); csl = torch.from_numpy(cnt_).to(dev)
+    prs = shard.pair_partition(F, 0, 1)
+    shard.sweep_pairs(dsl, csl, prs[:8], dev.index)
+    torch.cuda.synchronize(dev); e0.record(s)
+    acc = shard.sweep_pairs(dsl, csl, prs, dev.index)
+    e1.record(s); torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1)
+    dpairs = float((cnt_[prs[:, 0]].astype(np.float64) * cnt_[prs[:, 1]]).sum())
+    out["hamming_sweep_%d_frames" % F] = {"frame_pairs": int(len(prs)), "descriptor_pairs": dpairs, "ms": ms, "gpairs_per_s": dpairs / ms / 1e6,
+                                          "gops_per_s": 24 * dpairs / ms / 1e6, "accepted_matches": int(acc.sum().item())}
     return out
 
 
@@ -305,7 +331,7 @@ def run_ours(args, rank, world, local_rank):
     sweep = None
     if dist is not None:
         from os1_b200 import shard
-        Fl = min(8, B)
+        Fl = min(32, B)
         dsl = desc_d[:Fl].contiguous(); csl = cnt_d[:Fl].contiguous()
         shard.allgather_descriptors(dsl, csl)             # warm-up (NCCL channel set-up)
         barrier()
@@ -317,7 +343,7 @@ def run_ours(args, rank, world, local_rank):
         acc = shard.sweep_pairs(d_all, c_all, pairs, local_rank)
         s2.record(stream)
         barrier()
-        tg = torch.tensor([s0.elapsed_time(s1), s1.elapsed_time(s2), float(len(pairs)), float(acc.sum())], device=dev, dtype=torch.float64)
+        tg = torch.tensor([s0.elapsed_time(s1), s1.elapsed_time(s2), float(len(pairs)), float(acc.sum().item())], device=dev, dtype=torch.float64)
         tmax = tg.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = tg.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         npairs = int(tsum[2].item())
@@ -326,7 +352,8 @@ def run_ours(args, rank, world, local_rank):
                  "allgather_bytes_per_rank": int(dsl.numel() + csl.numel() * 4),
                  "match_ms": float(tmax[1].item()), "accepted_matches": int(tsum[3].item()),
                  "gpairs_per_s": npairs * cmean * cmean / (float(tmax[1].item()) * 1e-3) / 1e9,
-                 "note": "descriptor pairs/s over all ranks incl. per-pair launch + acceptance test; NCCL all_gather_into_tensor"}
+                 "gops_per_s": 24 * npairs * cmean * cmean / (float(tmax[1].item()) * 1e-3) / 1e9,
+                 "note": "descriptor pairs/s over all ranks, one batched launch per rank incl. the acceptance test; NCCL all_gather_into_tensor"}
 
     if dist is not None:
         dist.barrier()

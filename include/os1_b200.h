@@ -117,6 +117,15 @@ int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t
 int os1_hamming_window(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, int32_t* best_idx,
                        int32_t* best_dist, int32_t* second_dist, int on_device, int device, void* cuda_stream);
 
+/* Many all-pairs scans in one launch — the cross-keyframe sweep of BASELINE.json configs[4].  DEVICE pointers.
+ * desc: a slab of F descriptor sets, set f at desc + f*cap*32 with counts[f] valid rows; pairs: npairs x {i, j};
+ * for every pair the rows of set i are scanned against the whole of set j exactly as os1_hamming_knn2 does.
+ * best_idx / best_dist / second_dist: npairs x cap each (any of them may be NULL); accepted (may be NULL): per pair, the
+ * number of rows with best <= th_low && best < nnratio * second (the acceptance test of src/ORBmatcher.cc:454-456).
+ * Enqueues on cuda_stream and returns. */
+int os1_hamming_knn2_pairs(const uint8_t* desc, const int32_t* counts, int cap, const int32_t* pairs, int npairs, int32_t* best_idx,
+                           int32_t* best_dist, int32_t* second_dist, int32_t* accepted, float nnratio, int th_low, int device, void* cuda_stream);
+
 /* Distance of every entry of the candidate lists: dist[k] = DescriptorDistance(A[i], B[cand[k]]) for ptr[i] <= k < ptr[i+1]
  * (src/ORBmatcher.cc:1605-1621 evaluated for the whole of a matcher's scan in one launch). */
 int os1_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, uint16_t* dist,

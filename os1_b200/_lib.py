@@ -35,6 +35,7 @@ SYMBOLS = [
     ("os1_descriptor_distance", _i, [_vp, _vp]),
     ("os1_hamming_knn2", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp]),
     ("os1_hamming_knn2_noalloc", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _vp]),
+    ("os1_hamming_knn2_pairs", _i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _i, _i, _vp]),
     ("os1_hamming_csr", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp]),
     ("os1_search_for_initialization", _i, [_vp, _i, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp, C.POINTER(_i), _i]),
     ("os1_search_by_projection_frame", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_i), _i]),

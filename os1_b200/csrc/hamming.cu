@@ -17,8 +17,8 @@
 #include <climits>
 #include <mutex>
 
-#define HM_ROWS 128
-#define HM_TILE 256
+#define HM_ROWS 64
+#define HM_TILE 64
 #define HM_POSBITS 20
 #define HM_POSMASK ((1u << HM_POSBITS) - 1)
 #define HM_EMPTY 0xFFFFFFFFu
@@ -106,6 +106,52 @@ __global__ void __launch_bounds__(128) hamming_window_kernel(const uint4* __rest
     }
 }
 
+// Many frame pairs in one launch (the cross-frame sweep of BASELINE.json configs[4]): blockIdx.y selects the pair
+// (i, j) of a slab of per-frame descriptor sets; every thread scans the whole of frame j for its row of frame i, so
+// no partials or merge are needed.  `accepted[pair]` counts rows passing ORBmatcher's test
+// best <= th_low && best < nnratio * second  (src/ORBmatcher.cc:454-456).
+__global__ void __launch_bounds__(HM_ROWS) hamming_pairs_kernel(const uint4* __restrict__ desc, const int* __restrict__ counts, int cap,
+                                                                const int2* __restrict__ pairs, int* bestIdx, int* bestDist, int* secondDist,
+                                                                int* accepted, float nnratio, int thLow)
+{
+    __shared__ uint4 tile[HM_TILE * 2];
+    const int2 pr = pairs[blockIdx.y];
+    const int nA = counts[pr.x], nB = counts[pr.y];
+    if ((int)(blockIdx.x * HM_ROWS) >= nA) return;
+    const uint4* A = desc + (long long)pr.x * cap * 2;
+    const uint4* B = desc + (long long)pr.y * cap * 2;
+    const int row = blockIdx.x * HM_ROWS + threadIdx.x;
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+    if (row < nA) { a0 = __ldg(A + 2 * row); a1 = __ldg(A + 2 * row + 1); }
+    unsigned best = HM_EMPTY, second = HM_EMPTY;
+    for (int t0 = 0; t0 < nB; t0 += HM_TILE) {
+        const int cnt = min(HM_TILE, nB - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < cnt * 2; i += HM_ROWS) tile[i] = __ldg(B + 2 * (long long)t0 + i);
+        __syncthreads();
+#pragma unroll 4
+        for (int j = 0; j < cnt; j++) {
+            const unsigned k = ((unsigned)dist256(a0, a1, tile[2 * j], tile[2 * j + 1]) << HM_POSBITS) | (unsigned)(t0 + j);
+            second = min(second, max(k, best));
+            best = min(best, k);
+        }
+    }
+    int ok = 0;
+    if (row < nA) {
+        const int bd = best == HM_EMPTY ? INT_MAX : (int)(best >> HM_POSBITS);
+        const int sd = second == HM_EMPTY ? INT_MAX : (int)(second >> HM_POSBITS);
+        const long long o = (long long)blockIdx.y * cap + row;
+        if (bestIdx) bestIdx[o] = best == HM_EMPTY ? -1 : (int)(best & HM_POSMASK);
+        if (bestDist) bestDist[o] = bd;
+        if (secondDist) secondDist[o] = sd;
+        ok = bd <= thLow && (float)bd < __fmul_rn((float)sd, nnratio);
+    }
+    if (accepted) {
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(&accepted[blockIdx.y], __popc(m));
+    }
+}
+
 // dist[k] = distance(A[row of k], B[cand[k]]) for every CSR entry; one warp per row
 __global__ void __launch_bounds__(128) hamming_csr_kernel(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B,
                                                           const int* __restrict__ ptr, const int* __restrict__ cand, uint16_t* __restrict__ dist)
@@ -122,6 +168,23 @@ __global__ void __launch_bounds__(128) hamming_csr_kernel(const uint4* __restric
 
 } // namespace
 
+cudaError_t os1_launch_hamming_pairs(const uint8_t* desc, const int* counts, int cap, const int* pairs, int npairs, int* bestIdx, int* bestDist,
+                                     int* secondDist, int* accepted, float nnratio, int thLow, cudaStream_t s)
+{
+    if (npairs <= 0 || cap <= 0) return cudaSuccess;
+    if (cap > (int)HM_POSMASK) return cudaErrorInvalidValue;
+    if (accepted) { cudaError_t e = cudaMemsetAsync(accepted, 0, (size_t)npairs * 4, s); if (e != cudaSuccess) return e; }
+    for (int p0 = 0; p0 < npairs; p0 += 65535) {
+        const int n = min(65535, npairs - p0);
+        dim3 grid((cap + HM_ROWS - 1) / HM_ROWS, n);
+        const long long o = (long long)p0 * cap;
+        hamming_pairs_kernel<<<grid, HM_ROWS, 0, s>>>((const uint4*)desc, counts, cap, (const int2*)pairs + p0, bestIdx ? bestIdx + o : nullptr,
+                                                     bestDist ? bestDist + o : nullptr, secondDist ? secondDist + o : nullptr,
+                                                     accepted ? accepted + p0 : nullptr, nnratio, thLow);
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s)
 {
     if (nA <= 0) return cudaSuccess;
@@ -133,7 +196,7 @@ cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, c
 int os1_hamming_splits(int nA, int nB, int sms)
 {
     const int rowBlocks = (nA + HM_ROWS - 1) / HM_ROWS;
-    int s = (2 * sms + rowBlocks - 1) / rowBlocks;            // aim at ~2 CTAs per SM
+    int s = (8 * sms + rowBlocks - 1) / rowBlocks;            // aim at ~8 two-warp CTAs per SM: the scan is latency bound
     const int maxS = (nB + HM_TILE - 1) / HM_TILE;             // at least one tile per split
     if (s > maxS) s = maxS;
     if (s < 1) s = 1;

@@ -103,3 +103,5 @@ cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B
                                       int* bestDist, int* secondDist, cudaStream_t s);
 cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s);
 void os1_internal_set_error(const char* msg);
+cudaError_t os1_launch_hamming_pairs(const uint8_t* desc, const int* counts, int cap, const int* pairs, int npairs, int* bestIdx, int* bestDist,
+                                     int* secondDist, int* accepted, float nnratio, int thLow, cudaStream_t s);

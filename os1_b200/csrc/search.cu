@@ -95,6 +95,18 @@ int os1_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, int nB, const in
     return OS1_OK;
 }
 
+int os1_hamming_knn2_pairs(const uint8_t* desc, const int32_t* counts, int cap, const int32_t* pairs, int npairs, int32_t* best_idx,
+                           int32_t* best_dist, int32_t* second_dist, int32_t* accepted, float nnratio, int th_low, int device, void* cuda_stream)
+{
+    if (npairs < 0 || cap <= 0 || (npairs > 0 && (!desc || !counts || !pairs))) { os1_internal_set_error("os1_hamming_knn2_pairs: bad argument"); return OS1_E_INVALID; }
+    if (npairs == 0) return OS1_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = os1_launch_hamming_pairs(desc, counts, cap, pairs, npairs, best_idx, best_dist, second_dist, accepted, nnratio, th_low,
+                                                      (cudaStream_t)cuda_stream);
+    if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_hamming_knn2_pairs: CUDA failure (no CPU fallback)"); return OS1_E_CUDA; }
+    return OS1_OK;
+}
+
 int os1_search_for_initialization(const uint8_t* D1, int n1, const uint8_t* D2, int n2, const int32_t* ptr, const int32_t* cand, float nnratio,
                                   const float* angles1, const float* angles2, int32_t* matches12, int* nmatches, int device)
 {

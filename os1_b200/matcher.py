@@ -41,6 +41,13 @@ def hamming_knn2_noalloc_raw(a_ptr, nA, b_ptr, nB, bi_ptr, bd_ptr, sd_ptr, devic
     _lib.check(_lib.load().os1_hamming_knn2_noalloc(a_ptr, nA, b_ptr, nB, bi_ptr, bd_ptr, sd_ptr, device, stream))
 
 
+def hamming_knn2_pairs_raw(desc_ptr, counts_ptr, cap, pairs_ptr, npairs, bi_ptr, bd_ptr, sd_ptr, accepted_ptr, nnratio=0.9, th_low=TH_LOW,
+                           device=0, stream=None):
+    """os1_hamming_knn2_pairs: many frame-pair scans in one launch (device pointers; NULL outputs are skipped)."""
+    _lib.check(_lib.load().os1_hamming_knn2_pairs(desc_ptr, counts_ptr, cap, pairs_ptr, npairs, bi_ptr, bd_ptr, sd_ptr, accepted_ptr,
+                                                  nnratio, th_low, device, stream))
+
+
 def hamming_window(A, B, ptr, cand, device=0):
     """Best / second best over per-row candidate lists (CSR), e.g. the lists Frame::GetFeaturesInArea returns."""
     A = np.ascontiguousarray(A, np.uint8).reshape(-1, 32)

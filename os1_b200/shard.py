@@ -41,23 +41,17 @@ def allgather_descriptors(desc, counts, group=None):
 
 
 def sweep_pairs(desc_all, counts_all, pairs, device_index, th_low=50, nnratio=0.9):
-    """Matches every (i, j) of `pairs` with the all-pairs Hamming kernel (device tensors); returns the number of
-    accepted matches per pair under ORBmatcher's test best <= TH_LOW and best < nnratio * second
+    """Matches every (i, j) of `pairs` in ONE launch of the batched Hamming kernel (device tensors); returns the number
+    of accepted matches per pair under ORBmatcher's test best <= TH_LOW and best < nnratio * second
     (src/ORBmatcher.cc:454-456)."""
     import torch
     from . import matcher
     dev = desc_all.device
     cap = desc_all.shape[1]
-    bi = torch.empty(cap, dtype=torch.int32, device=dev); bd = torch.empty_like(bi); sd = torch.empty_like(bi)
-    counts = counts_all.cpu().numpy()
-    out = np.zeros(len(pairs), np.int64)
+    p = torch.as_tensor(np.ascontiguousarray(pairs, np.int32)).to(dev)
+    acc = torch.zeros(max(len(pairs), 1), dtype=torch.int32, device=dev)
+    c32 = counts_all.to(torch.int32).contiguous()
     stream = torch.cuda.current_stream(dev).cuda_stream
-    acc = torch.zeros(len(pairs), dtype=torch.int64, device=dev)
-    for k, (i, j) in enumerate(pairs):
-        nA, nB = int(counts[i]), int(counts[j])
-        matcher.hamming_knn2_raw(desc_all[i].data_ptr(), nA, desc_all[j].data_ptr(), nB, bi.data_ptr(), bd.data_ptr(), sd.data_ptr(),
-                                 device=device_index, stream=stream)
-        ok = (bd[:nA] <= th_low) & (bd[:nA].float() < nnratio * sd[:nA].float())
-        acc[k] = ok.sum()
-    out[:] = acc.cpu().numpy()
-    return out
+    matcher.hamming_knn2_pairs_raw(desc_all.data_ptr(), c32.data_ptr(), cap, p.data_ptr(), len(pairs), None, None, None, acc.data_ptr(),
+                                   nnratio, th_low, device=device_index, stream=stream)
+    return acc[:len(pairs)]

@@ -52,3 +52,27 @@ def test_window_matches_oracle(oracle_lib):
     for g, r in zip(got, ref):
         assert np.array_equal(g, r)
     assert got[0][3] == -1
+
+
+def test_pairs_batch_matches_per_pair_oracle(oracle_lib):
+    """os1_hamming_knn2_pairs: several frame pairs in one launch == the single-pair scan on each, plus the accepted count."""
+    import torch
+    import os1_b200
+    fr = synth.video(4, 480, 640, seed=3)
+    e = os1_b200.ORBextractor(1000, 1.2, 8, 20, 7)
+    kp, desc, cnt = e.extract_batch(fr)
+    cap = desc.shape[1]
+    pairs = np.array([[0, 1], [0, 2], [1, 3], [2, 3], [3, 0]], np.int32)
+    d = torch.from_numpy(desc).cuda(); c = torch.from_numpy(cnt).cuda(); p = torch.from_numpy(pairs).cuda()
+    bi = torch.full((len(pairs), cap), -9, dtype=torch.int32, device="cuda"); bd = torch.zeros_like(bi); sd = torch.zeros_like(bi)
+    acc = torch.zeros(len(pairs), dtype=torch.int32, device="cuda")
+    matcher.hamming_knn2_pairs_raw(d.data_ptr(), c.data_ptr(), cap, p.data_ptr(), len(pairs), bi.data_ptr(), bd.data_ptr(), sd.data_ptr(),
+                                   acc.data_ptr(), 0.9, 50)
+    torch.cuda.synchronize()
+    for k, (i, j) in enumerate(pairs):
+        ri, rd, rs = oracle_lib.Oracle.hamming_knn2(desc[i, :cnt[i]], desc[j, :cnt[j]])
+        n = cnt[i]
+        assert np.array_equal(bi[k, :n].cpu().numpy(), ri) and np.array_equal(bd[k, :n].cpu().numpy(), rd)
+        assert np.array_equal(sd[k, :n].cpu().numpy(), rs)
+        ok = (rd <= 50) & (rd.astype(np.float32) < rs.astype(np.float32) * np.float32(0.9))
+        assert int(acc[k]) == int(ok.sum())
