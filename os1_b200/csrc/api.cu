@@ -527,6 +527,10 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     auto stage_in = [&](int f0, int n, cudaStream_t st) -> cudaError_t {
         const uint8_t* src = frames + (size_t)f0 * frame_stride;
         uint8_t* dst = slab + (long long)f0 * g.slabBytes + L0.off;
+        if ((size_t)L0.pitch == step) {
+            // same row pitch on both sides: a frame is one contiguous run, the batch a 2-D copy of long rows
+            return cudaMemcpy2DAsync(dst, (size_t)g.slabBytes, src, frame_stride, (size_t)(rows - 1) * step + cols, n, inKind, st);
+        }
         if (n > 1 && frame_stride % step == 0 && g.slabBytes % L0.pitch == 0) {
             cudaMemcpy3DParms p;
             memset(&p, 0, sizeof(p));
@@ -581,9 +585,17 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
 
     // ---- batches with host buffers: chunks flow through upload -> kernels -> download on three streams, so the PCIe
     // copies of neighbouring chunks hide behind the kernels of the current one ----------------------------------------------
-    int chunk = 32;
+    int chunk = 64;
     if (const char* e = getenv("OS1_CHUNK")) chunk = std::max(1, atoi(e));
-    const int nchunks = (nframes + chunk - 1) / chunk;
+    // chunk boundaries: the first two chunks are a quarter and a half of the steady size, so the kernels start after a
+    // short upload instead of idling through a full one
+    std::vector<int> cuts(1, 0);
+    for (int f = 0, c = 0; f < nframes; c++) {
+        const int sz = std::max(1, c == 0 ? chunk / 4 : (c == 1 ? chunk / 2 : chunk));
+        f = std::min(nframes, f + sz);
+        cuts.push_back(f);
+    }
+    const int nchunks = (int)cuts.size() - 1;
     if (!h->inStream) CK(cudaStreamCreateWithFlags(&h->inStream, cudaStreamNonBlocking), "cudaStreamCreate");
     if (!h->outStream) CK(cudaStreamCreateWithFlags(&h->outStream, cudaStreamNonBlocking), "cudaStreamCreate");
     while ((int)h->chunkEv.size() < 2 * nchunks + 1) {
@@ -598,7 +610,7 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     const size_t kpRow = (size_t)dCap * sizeof(os1_kp_dev), dRow = (size_t)dCap * 32;
     const int copyCap = std::min(dCap, cap_per_frame);
     for (int c = 0; c < nchunks; c++) {
-        const int f0 = c * chunk, n = std::min(chunk, nframes - f0);
+        const int f0 = cuts[c], n = cuts[c + 1] - cuts[c];
         if (!direct) {
             CK(stage_in(f0, n, frames_on_device ? h->stream : h->inStream), "upload frames");
             if (!frames_on_device) {
