@@ -556,7 +556,7 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
         return run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, nframes, dKp, dDesc, dCap, dCnt);
     }
 
-    // ---- one frame from the host: the latency path (fetch the count, then only what was produced) -----------------------
+    // ---- one frame from the host: the latency path --------------------------------------------------------------------------
     if (nframes == 1 && !out_on_device) {
         if (!direct) CK(stage_in(0, 1, h->stream), "upload frame");
         rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, 1, dKp, dDesc, dCap, dCnt);
@@ -565,17 +565,17 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
         os1_kp_dev* hk = (os1_kp_dev*)hb;
         uint8_t* hd = hb + (size_t)cap * sizeof(os1_kp_dev);
         int* hc = (int*)(hd + (size_t)cap * 32);
+        // one round trip: the count, the status word and the (small, fixed-size) output slabs travel together
         CK(cudaMemcpyAsync(hc, dCnt, 4, cudaMemcpyDeviceToHost, h->stream), "download count");
         CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
+        CK(cudaMemcpyAsync(hk, dKp, (size_t)cap * sizeof(os1_kp_dev), cudaMemcpyDeviceToHost, h->stream), "download keypoints");
+        CK(cudaMemcpyAsync(hd, dDesc, (size_t)cap * 32, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
         CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
         rc = check_status(h, h->hostStatus[0]);
         if (rc) return rc;
         const int n = std::min(hc[0], cap);
         if (n > cap_per_frame) return fail(h, OS1_E_CAPACITY, "os1_orb_extract: caller capacity smaller than the keypoint count (see os1_orb_max_keypoints)");
         if (n > 0) {
-            CK(cudaMemcpyAsync(hk, dKp, (size_t)n * sizeof(os1_kp_dev), cudaMemcpyDeviceToHost, h->stream), "download keypoints");
-            CK(cudaMemcpyAsync(hd, dDesc, (size_t)n * 32, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
-            CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
             memcpy(kp, hk, (size_t)n * sizeof(os1_keypoint));
             memcpy(desc, hd, (size_t)n * 32);
         }

@@ -19,7 +19,6 @@
 // Tie rule for equal-size nodes: later-created first (DESIGN.md "canonical tie rule").
 #include "os1_internal.cuh"
 
-#define QT_THREADS 512
 #define QT_DONE 0xFFFFu
 #define QT_LEAF 0x80000000u
 
@@ -31,6 +30,7 @@ struct QtParams {
     int maxNodes, maxLeaves, maxCells, sortCap;
 };
 
+template <int QT_THREADS>
 __device__ __forceinline__ int block_scan_excl(int v, int* warpSums, int& total)
 {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -60,6 +60,7 @@ __device__ __forceinline__ int block_scan_excl(int v, int* warpSums, int& total)
 }
 
 // in-place bitonic sort of n64 (power of two) keys, descending when desc != 0
+template <int QT_THREADS>
 __device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
 {
     for (int k = 2; k <= n; k <<= 1)
@@ -76,7 +77,8 @@ __device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
         }
 }
 
-__global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_constant__ QtParams P)
+template <int QT_THREADS>
+__global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel(const __grid_constant__ QtParams P)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
     const Geometry& g = P.g;
@@ -123,7 +125,7 @@ __global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_co
             int c = base + tid;
             int v = (c < L.nCells) ? (int)cellCnt[c] : 0;
             int tot;
-            int ex = block_scan_excl(v, warpSums, tot);
+            int ex = block_scan_excl<QT_THREADS>(v, warpSums, tot);
             if (c < L.nCells) cellOffs[c] = carry + ex;
             carry += tot;
         }
@@ -148,14 +150,22 @@ __global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_co
     const int nIni = L.nIni;
     for (int i = tid; i < 4 * P.maxNodes; i += QT_THREADS) slotCnt[i] = 0;
     __syncthreads();
-    for (int base = 0; base < n; base += QT_THREADS) {
-        const int i = base + tid;
-        const bool valid = i < n;
-        const unsigned m = __ballot_sync(0xffffffffu, valid);
-        if (valid) {
-            const int r = code[i] >> (2 * D);
-            const unsigned grp = __match_any_sync(m, r);
-            if (lane == __ffs(grp) - 1) atomicAdd(&slotCnt[r], __popc(grp));
+    for (int base = 0; base < n; base += 4 * QT_THREADS) {
+        uint32_t cd[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = base + u * QT_THREADS + tid;
+            cd[u] = i < n ? code[i] : 0xFFFFFFFFu;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const bool valid = cd[u] != 0xFFFFFFFFu;
+            const unsigned m = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                const int r = cd[u] >> (2 * D);
+                const unsigned grp = __match_any_sync(m, r);
+                if (lane == __ffs(grp) - 1) atomicAdd(&slotCnt[r], __popc(grp));
+            }
         }
     }
     __syncthreads();
@@ -207,7 +217,7 @@ __global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_co
             for (int j = tid; j < n2; j += QT_THREADS)
                 sortBuf[j] = (j < E) ? (((unsigned long long)curSize[j] << 32) | ((unsigned long long)(curKey[j] & 0xFFFFu) << 16) | (unsigned)j) : 0ull;
             __syncthreads();
-            bitonic_sort(sortBuf, n2, true);
+            bitonic_sort<QT_THREADS>(sortBuf, n2, true);
             for (int p = tid; p < E; p += QT_THREADS) {
                 int j = (int)(sortBuf[p] & 0xFFFFu);
                 order[p] = j; procPos[j] = p;
@@ -217,16 +227,24 @@ __global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_co
         __syncthreads();
 
         // sweep A: children sizes
-        for (int base = 0; base < n; base += QT_THREADS) {
-            const int i = base + tid;
-            int nd = QT_DONE;
-            if (i < n) nd = node[i];
-            const bool valid = nd != QT_DONE;
-            const unsigned m = __ballot_sync(0xffffffffu, valid);
-            if (valid) {
-                const int slot = nd * 4 + ((code[i] >> shift) & 3);
-                const unsigned grp = __match_any_sync(m, slot);
-                if (lane == __ffs(grp) - 1) atomicAdd(&slotCnt[slot], __popc(grp));
+        // (four candidates per thread per trip: the eight loads are in flight together — the sweeps are latency bound)
+        for (int base = 0; base < n; base += 4 * QT_THREADS) {
+            int nd[4]; uint32_t cd[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = base + u * QT_THREADS + tid;
+                nd[u] = i < n ? (int)node[i] : (int)QT_DONE;
+                cd[u] = i < n ? code[i] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bool valid = nd[u] != QT_DONE;
+                const unsigned m = __ballot_sync(0xffffffffu, valid);
+                if (valid) {
+                    const int slot = nd[u] * 4 + ((cd[u] >> shift) & 3);
+                    const unsigned grp = __match_any_sync(m, slot);
+                    if (lane == __ffs(grp) - 1) atomicAdd(&slotCnt[slot], __popc(grp));
+                }
             }
         }
         __syncthreads();
@@ -243,8 +261,8 @@ __global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_co
                     for (int q = 0; q < 4; q++) { uint32_t c = slotCnt[4 * j + q]; nz += (c > 0); mz += (c > 1); }
                 }
                 int tn, tm;
-                int en = block_scan_excl(nz, warpSums, tn);
-                int em = block_scan_excl(mz, warpSums, tm);
+                int en = block_scan_excl<QT_THREADS>(nz, warpSums, tn);
+                int em = block_scan_excl<QT_THREADS>(mz, warpSums, tm);
                 if (p < E) { nzCum[p] = carryN + en; mzCum[p] = carryM + em; }
                 carryN += tn; carryM += tm;
             }
@@ -307,18 +325,28 @@ __global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_co
         __syncthreads();
 
         // sweep B: re-label candidates / vote for the best response of finished leaves
-        for (int i = tid; i < n; i += QT_THREADS) {
-            const int nd = node[i];
-            if (nd == QT_DONE) continue;
-            if ((int)procPos[nd] >= nSplit) {
-                atomicMax(&leafBest[unsplitLeaf[nd]], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
-                node[i] = QT_DONE;
-            } else {
-                const uint32_t info = slotInfo[nd * 4 + ((code[i] >> shift) & 3)];
-                if (info & QT_LEAF) {
-                    atomicMax(&leafBest[info & 0xFFFF], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
+        for (int base = 0; base < n; base += 4 * QT_THREADS) {
+            int nd[4]; uint32_t cd[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i = base + u * QT_THREADS + tid;
+                nd[u] = i < n ? (int)node[i] : (int)QT_DONE;
+                cd[u] = i < n ? code[i] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (nd[u] == QT_DONE) continue;
+                const int i = base + u * QT_THREADS + tid;
+                if ((int)procPos[nd[u]] >= nSplit) {
+                    atomicMax(&leafBest[unsplitLeaf[nd[u]]], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
                     node[i] = QT_DONE;
-                } else node[i] = (uint16_t)info;
+                } else {
+                    const uint32_t info = slotInfo[nd[u] * 4 + ((cd[u] >> shift) & 3)];
+                    if (info & QT_LEAF) {
+                        atomicMax(&leafBest[info & 0xFFFF], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
+                        node[i] = QT_DONE;
+                    } else node[i] = (uint16_t)info;
+                }
             }
         }
         __syncthreads();
@@ -336,7 +364,7 @@ __global__ void __launch_bounds__(QT_THREADS, 2) quadtree_kernel(const __grid_co
         for (int j = tid; j < n2; j += QT_THREADS)
             sortBuf[j] = (j < nLeaves) ? (((unsigned long long)leafKey[j] << 32) | leafBest[j]) : ~0ull;
         __syncthreads();
-        bitonic_sort(sortBuf, n2, false);
+        bitonic_sort<QT_THREADS>(sortBuf, n2, false);
         if (nLeaves > L.kpCap) { if (tid == 0) atomicOr(P.d.status, OS1_ERR_KP_OVERFLOW); nLeaves = L.kpCap; }
         for (int j = tid; j < nLeaves; j += QT_THREADS) {
             const uint32_t best = (uint32_t)sortBuf[j];
@@ -364,11 +392,20 @@ cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes
     size_t smem = (size_t)P.sortCap * 8 + (size_t)(P.maxCells + 1) * 4 + (size_t)P.maxNodes * 4 * (4 + 4 + 2 + 2 + 1 + 1 + 1 + 1 + 1) + 8 * 4 +
                   (size_t)P.maxLeaves * 8 + 34 * 4;
     if (smem > 220 * 1024 || P.maxNodes > 16000) return cudaErrorNotSupported;
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(quadtree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-    }
     dim3 grid(g.nlevels, nframes);
-    quadtree_kernel<<<grid, QT_THREADS, smem, s>>>(P);
+    // few frames: the level-0 CTA is the critical path, give it 1024 threads; batches: 512 threads, two CTAs per SM
+    if (nframes <= 4) {
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(quadtree_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+        }
+        quadtree_kernel<1024><<<grid, 1024, smem, s>>>(P);
+    } else {
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(quadtree_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+        }
+        quadtree_kernel<512><<<grid, 512, smem, s>>>(P);
+    }
     return cudaGetLastError();
 }
