@@ -194,13 +194,18 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constan
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
 
+    const int ng = g1 - g0, nItems = ng * (tr1 - tr0);
+    const unsigned rcpNg = (1u << 24) / (unsigned)ng + 1u;          // exact quotient for idx < 2^16 (nItems <= 136 * 64)
     // stored s8 = strength - tmin; response = strength - 1 = s8 + tmin - 1
     const int iniS8 = g.iniTh - tmin + 1, minS8 = g.minTh - tmin + 1;
     // ---- phase 2: scores, four pixels per thread, kept packed ---------------------------------------------------------
     {
         const unsigned T = (unsigned)tmin * 0x01010101u;       // tmin * 257 in both lanes
-        for (int r = tr0 + warp; r < tr1; r += FAST_THREADS / 32)
-            for (int gq = g0 + lane; gq < g1; gq += 32) {
+        // (rows x groups flattened so that every lane has work: 75 groups per row would leave a third of the lanes
+        //  idle in the last of three 32-wide trips; the division by the group count is a multiply by its reciprocal)
+        for (int idx = tid; idx < nItems; idx += FAST_THREADS) {
+                const int rr = (int)(((unsigned)idx * rcpNg) >> 24);
+                const int r = tr0 + rr, gq = g0 + idx - rr * ng;
                 unsigned W[7][3];
                 const unsigned* row = img + (r - 3) * pw + gq;
 #pragma unroll
@@ -222,8 +227,9 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constan
     __syncthreads();
 
     // ---- phase 3: NMS on the packed maps; survivors go to their cell's list ----------------------------------------------
-    for (int r = tr0 + warp; r < tr1; r += FAST_THREADS / 32)
-        for (int gq = g0 + lane; gq < g1; gq += 32) {
+    for (int idx = tid; idx < nItems; idx += FAST_THREADS) {
+            const int rr = (int)(((unsigned)idx * rcpNg) >> 24);
+            const int r = tr0 + rr, gq = g0 + idx - rr * ng;
             const int o = r * pw + gq;
             const unsigned vE = scE[o], vO = scO[o];
             if ((vE | vO) == 0) continue;
@@ -266,32 +272,34 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constan
 
     // ---- phase 4: per cell — the >= iniTh list if it is not empty, else the weaker one (the reference's retry with
     // minThFAST, ORBextractor.cc:852-856); rank by (row, column) by counting; emit in cv::FAST's order -----------------
-    for (int cc = 0; cc < ncell; cc++) {
+    for (int cc = warp; cc < ncell; cc += FAST_THREADS / 32) {          // one warp per cell, lanes = survivors
         const int nA = s_n[0][cc], nB = s_n[1][cc];
-        if (nA + nB > listCap && tid == 0) atomicOr(P.d.status, OS1_ERR_CELL_OVERFLOW);
+        if (nA + nB > listCap && lane == 0) atomicOr(P.d.status, OS1_ERR_CELL_OVERFLOW);
         const int which = nA > 0 ? 0 : 1;
-        // with iniTh <= minTh the retry adds nothing: the weaker list then only holds responses below minTh... which
-        // cannot exist (tmin = iniTh), so the rule above still reproduces the reference
+        // with iniTh <= minTh the retry adds nothing: the weaker list is then empty (tmin = iniTh), so the rule above
+        // still reproduces the reference
         const int n = min(which ? nB : nA, listCap);
         const unsigned* lst = lists + cc * listCap + (which ? listCap - n : 0);
         uint32_t* out = P.d.stage + (long long)frame * g.candPerFrame + L.candOff + (long long)(ci * L.nCols + j0 + cc) * L.cellCap;
-        for (int i = tid; i < n; i += FAST_THREADS) {
-            const unsigned e = lst[i];
-            if (which && (int)(e & 0xFF) < minS8) continue;
+        const int lim = which ? minS8 : 0;                                 // every entry of the strong list passes
+        int emitted = 0;
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            const int i = i0 + lane;
+            const unsigned e = i < n ? lst[i] : 0u;
+            const bool pass = i < n && (int)(e & 0xFF) >= lim;
             int rank = 0;
             for (int j = 0; j < n; j++) {
-                const unsigned f = lst[j];
-                rank += (f < e) && (!which || (int)(f & 0xFF) >= minS8);
+                const unsigned f = lst[j];                                  // broadcast read
+                rank += (f < e) && ((int)(f & 0xFF) >= lim);
             }
-            const int r = e >> 22, col = (e >> 8) & 0x3FFF;
-            if (rank < L.cellCap)
-                out[rank] = OS1_PACK_XYS(col + xorg - OS1_BORDER, r + y0 - OS1_BORDER, (int)(e & 0xFF) + tmin - 1);
+            if (pass) {
+                const int r = e >> 22, col = (e >> 8) & 0x3FFF;
+                if (rank < L.cellCap)
+                    out[rank] = OS1_PACK_XYS(col + xorg - OS1_BORDER, r + y0 - OS1_BORDER, (int)(e & 0xFF) + tmin - 1);
+            }
+            emitted += __popc(__ballot_sync(0xffffffffu, pass));
         }
-        if (tid == 0) {
-            int cnt = n;
-            if (which) { cnt = 0; for (int j = 0; j < n; j++) cnt += (int)(lst[j] & 0xFF) >= minS8; }
-            cellCnt[cc] = min(cnt, L.cellCap);
-        }
+        if (lane == 0) cellCnt[cc] = min(emitted, L.cellCap);
     }
 }
 
