@@ -153,6 +153,17 @@ int os1_search_by_projection_frame(const uint8_t* Dq, int nq, const uint8_t* Dc,
 int os1_search_by_projection_points(const uint8_t* Dq, int nq, const uint8_t* Dc, int nc, const int32_t* ptr, const int32_t* cand,
                                     uint8_t* taken, const int32_t* octave_c, float nnratio, int32_t* match_of_cand, int* nmatches, int device);
 
+/* Frame::AssignFeaturesToGrid + Frame::GetFeaturesInArea for a batch of queries (src/Frame.cc:114-129, :209-274):
+ * the 64 x 48 grid over [min_x, max_x) x [min_y, max_y) (Frame::ComputeImageBounds' mnMinX..mnMaxY), a keypoint's cell by
+ * PosInGrid's round(), and for query q the keypoints with |dx| < r, |dy| < r whose octave passes the reference's
+ * minLevel/maxLevel test (NULL arrays = -1 = no test), in the reference's visiting order (grid column, grid row, keypoint
+ * index).  kp: the frame's (undistorted) keypoints.  Output CSR: ptr[nq+1], cand[ptr[nq]]; if cand_cap is too small the call
+ * returns OS1_E_CAPACITY with the required size in ptr[nq] (host mode; device mode leaves ptr[nq] for the caller to check).
+ * on_device: every pointer is device memory and the work is only enqueued.  At most 16384 keypoints. */
+int os1_features_in_area(const os1_keypoint* kp, int n, float min_x, float max_x, float min_y, float max_y, const float* qx, const float* qy,
+                         const float* qr, const int32_t* q_min_level, const int32_t* q_max_level, int nq, int32_t* ptr, int32_t* cand,
+                         int cand_cap, int on_device, int device, void* cuda_stream);
+
 /* os1_hamming_knn2 for callers that must not allocate.  This entry point has no counterpart in the reference
  * (os1 has no GPU code and so no allocation policy to mirror); it exists for the hosts this library gets embedded in.
  *

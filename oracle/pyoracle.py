@@ -68,6 +68,7 @@ class Oracle:
             L.orc_hamming_knn2_mt.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _i]
             L.orc_hamming_window.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
             L.orc_search_for_initialization.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp]
+            L.orc_features_in_area.argtypes = [_vp, _vp, _i, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i]
             L.orc_search_by_projection_frame.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
             L.orc_search_by_projection_points.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp]
             cls._lib = L
@@ -190,6 +191,20 @@ class Oracle:
         n = cls.lib().orc_search_for_initialization(_p(D1), len(D1), _p(D2), len(D2), _p(ptr), _p(cand), nnratio,
                                                      None if a1 is None else _p(a1), None if a2 is None else _p(a2), _p(m))
         return n, m
+
+    @classmethod
+    def features_in_area(cls, xy, octave, bounds, qx, qy, qr, min_level=None, max_level=None):
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2); octave = np.ascontiguousarray(octave, np.int32)
+        qx = np.ascontiguousarray(qx, np.float32); qy = np.ascontiguousarray(qy, np.float32); qr = np.ascontiguousarray(qr, np.float32)
+        lo = None if min_level is None else np.ascontiguousarray(min_level, np.int32)
+        hi = None if max_level is None else np.ascontiguousarray(max_level, np.int32)
+        nq = len(qx)
+        ptr = np.zeros(nq + 1, np.int32)
+        cap = len(xy) * max(nq, 1) + 1
+        cand = np.zeros(cap, np.int32)
+        tot = cls.lib().orc_features_in_area(_p(xy), _p(octave), len(xy), bounds[0], bounds[1], bounds[2], bounds[3], _p(qx), _p(qy), _p(qr),
+                                             None if lo is None else _p(lo), None if hi is None else _p(hi), nq, _p(ptr), _p(cand), cap)
+        return ptr, cand[:tot].copy()
 
     @classmethod
     def search_by_projection_frame(cls, Dq, Dc, ptr, cand, taken, angles_q=None, angles_c=None):

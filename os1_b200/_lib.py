@@ -40,6 +40,7 @@ SYMBOLS = [
     ("os1_search_for_initialization", _i, [_vp, _i, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp, C.POINTER(_i), _i]),
     ("os1_search_by_projection_frame", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_i), _i]),
     ("os1_search_by_projection_points", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp, C.POINTER(_i), _i]),
+    ("os1_features_in_area", _i, [_vp, _i, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp]),
     ("os1_hamming_window", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
 ]
 

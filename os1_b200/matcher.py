@@ -113,3 +113,27 @@ def SearchByProjectionPoints(Dq, Dc, ptr, cand, taken, octave_c, nnratio=0.8, de
     _lib.check(_lib.load().os1_search_by_projection_points(_ptr(Dq), len(Dq), _ptr(Dc), len(Dc), _ptr(ptr), _ptr(cand), _ptr(taken),
                                                             _ptr(octave_c), nnratio, _ptr(m), C.byref(n), device))
     return n.value, m[:len(Dc)]
+
+
+def GetFeaturesInArea(kp, bounds, qx, qy, qr, min_level=None, max_level=None, device=0):
+    """Frame::GetFeaturesInArea (Frame.cc:209-262) for a batch of queries over the frame's 64x48 grid
+    (AssignFeaturesToGrid, Frame.cc:114-129).  kp: structured keypoint array (KEYPOINT_DTYPE); bounds = (mnMinX, mnMaxX,
+    mnMinY, mnMaxY).  Returns CSR (ptr, cand) in the reference's visiting order."""
+    kp = np.ascontiguousarray(kp)
+    qx = np.ascontiguousarray(qx, np.float32); qy = np.ascontiguousarray(qy, np.float32); qr = np.ascontiguousarray(qr, np.float32)
+    nq = len(qx)
+    lo = None if min_level is None else np.ascontiguousarray(min_level, np.int32)
+    hi = None if max_level is None else np.ascontiguousarray(max_level, np.int32)
+    ptr = np.zeros(nq + 1, np.int32)
+    cap = max(64 * nq, 1024)
+    L = _lib.load()
+    while True:
+        cand = np.zeros(cap, np.int32)
+        rc = L.os1_features_in_area(_ptr(kp), len(kp), bounds[0], bounds[1], bounds[2], bounds[3], _ptr(qx), _ptr(qy), _ptr(qr),
+                                    None if lo is None else _ptr(lo), None if hi is None else _ptr(hi), nq, _ptr(ptr), _ptr(cand), cap, 0,
+                                    device, None)
+        if rc == _lib.OS1_E_CAPACITY and ptr[nq] > cap:
+            cap = int(ptr[nq])
+            continue
+        _lib.check(rc)
+        return ptr, cand[:ptr[nq]].copy()

@@ -1,0 +1,75 @@
+"""GPU: Frame::AssignFeaturesToGrid + Frame::GetFeaturesInArea for a batch of queries, against the oracle's restatement
+of src/Frame.cc:114-129, :209-274 — candidate sets AND their order must be identical (the order decides ties in the
+matchers' first-seen rule)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from os1_b200 import matcher, synth  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def frame_kp():
+    import os1_b200
+    e = os1_b200.ORBextractor(2000, 1.2, 8, 20, 7)
+    k, d = e(synth.frame(720, 1280, 3))
+    return k, d
+
+
+def run_both(oracle_lib, k, bounds, qx, qy, qr, lo=None, hi=None):
+    ptr, cand = matcher.GetFeaturesInArea(k, bounds, qx, qy, qr, lo, hi)
+    xy = np.stack([k["x"], k["y"]], 1)
+    rptr, rcand = oracle_lib.Oracle.features_in_area(xy, k["octave"], bounds, qx, qy, qr, lo, hi)
+    assert np.array_equal(ptr, rptr) and np.array_equal(cand, rcand)
+    return ptr, cand
+
+
+def test_initialization_windows(oracle_lib, frame_kp):
+    k, _ = frame_kp
+    # SearchForInitialization: window 100 around every level-0 keypoint, levels 0..0 (ORBmatcher.cc:420)
+    q = k[k["octave"] == 0]
+    z = np.zeros(len(q), np.int32)
+    ptr, cand = run_both(oracle_lib, k, (0.0, 1280.0, 0.0, 720.0), q["x"], q["y"], np.full(len(q), 100, np.float32), z, z)
+    assert ptr[-1] > 10 * len(q) and (k["octave"][cand] == 0).all()
+
+
+def test_projection_windows_levels_and_borders(oracle_lib, frame_kp):
+    k, _ = frame_kp
+    rng = np.random.default_rng(4)
+    nq = 3000
+    qx = rng.uniform(-80, 1360, nq).astype(np.float32); qy = rng.uniform(-60, 780, nq).astype(np.float32)     # some far outside
+    lv = rng.integers(0, 8, nq).astype(np.int32)
+    qr = (15 * 1.2 ** lv).astype(np.float32)
+    ptr, cand = run_both(oracle_lib, k, (0.0, 1280.0, 0.0, 720.0), qx, qy, qr, lv - 1, lv + 1)       # levels oct-1..oct+1 (:1349)
+    assert (np.diff(ptr) == 0).any() and (np.diff(ptr) > 0).any()
+    run_both(oracle_lib, k, (0.0, 1280.0, 0.0, 720.0), qx[:500], qy[:500], qr[:500])                 # no level test at all
+    run_both(oracle_lib, k, (0.0, 1280.0, 0.0, 720.0), qx[:500], qy[:500], qr[:500], np.full(500, -1, np.int32), lv[:500])   # maxLevel only
+
+
+def test_undistorted_bounds_and_empty_inputs(oracle_lib, frame_kp):
+    k, _ = frame_kp
+    rng = np.random.default_rng(5)
+    qx = rng.uniform(0, 1280, 200).astype(np.float32); qy = rng.uniform(0, 720, 200).astype(np.float32)
+    qr = np.full(200, 40, np.float32)
+    run_both(oracle_lib, k, (-37.5, 1301.25, -12.0, 741.5), qx, qy, qr)            # bounds as ComputeImageBounds gives them after undistortion
+    ptr, cand = matcher.GetFeaturesInArea(k[:0], (0.0, 1280.0, 0.0, 720.0), qx, qy, qr)
+    assert ptr[-1] == 0 and len(cand) == 0
+    ptr, cand = matcher.GetFeaturesInArea(k, (0.0, 1280.0, 0.0, 720.0), qx[:0], qy[:0], qr[:0])
+    assert len(ptr) == 1 and ptr[0] == 0
+
+
+def test_grid_to_matcher_pipeline(oracle_lib, frame_kp):
+    """Candidate lists from the GPU grid feed SearchForInitialization directly (frame against a shifted copy)."""
+    import os1_b200
+    fr = synth.video(2, 720, 1280, seed=8, max_shift=10)
+    e = os1_b200.ORBextractor(2000, 1.2, 8, 20, 7)
+    k0, d0 = e(fr[0]); k1, d1 = e(fr[1])
+    lvl0 = k0["octave"] == 0
+    z = np.zeros(len(k0), np.int32)
+    r = np.where(lvl0, 100, 0).astype(np.float32)          # level > 0 queries are skipped by the reference (:415-417): r = 0 -> no candidate
+    ptr, cand = matcher.GetFeaturesInArea(k1, (0.0, 1280.0, 0.0, 720.0), k0["x"], k0["y"], r, z, z)
+    assert (np.diff(ptr)[~lvl0] == 0).all()
+    n, m = matcher.SearchForInitialization(d0, d1, ptr, cand, 0.9, k0["angle"], k1["angle"])
+    rn, rm = oracle_lib.Oracle.search_for_initialization(d0, d1, ptr, cand, 0.9, k0["angle"], k1["angle"])
+    assert n == rn and np.array_equal(m, rm[:len(m)]) and n > 100
