@@ -164,6 +164,15 @@ int os1_features_in_area(const os1_keypoint* kp, int n, float min_x, float max_x
                          const float* qr, const int32_t* q_min_level, const int32_t* q_max_level, int nq, int32_t* ptr, int32_t* cand,
                          int cand_cap, int on_device, int device, void* cuda_stream);
 
+/* Frame::UndistortKeyPoints (src/Frame.cc:286-320).  K4 = {fx, fy, cx, cy}.  mode 0 = pinhole: cv::undistortPoints(pts, pts, K,
+ * dist, Mat(), K) with dist = k1,k2,p1,p2[,k3[,k4,k5,k6[,s1..s4]]] (ndist values), the identity when dist[0] == 0 (:288-292);
+ * mode 1 = os1's equidistant fisheye without distortion (antidistorsionarProyeccionEquidistante, :355-384; dist ignored).
+ * kp_un receives copies of the keypoints with pt replaced (kp_un may alias kp). */
+int os1_undistort_keypoints(const os1_keypoint* kp, int n, const float* K4, const float* dist, int ndist, int mode, os1_keypoint* kp_un,
+                            int on_device, int device, void* cuda_stream);
+/* Frame::ComputeImageBounds (src/Frame.cc:322-353): bounds4 = {mnMinX, mnMaxX, mnMinY, mnMaxY}. */
+int os1_image_bounds(int cols, int rows, const float* K4, const float* dist, int ndist, int mode, float* bounds4, int device);
+
 /* os1_hamming_knn2 for callers that must not allocate.  This entry point has no counterpart in the reference
  * (os1 has no GPU code and so no allocation policy to mirror); it exists for the hosts this library gets embedded in.
  *

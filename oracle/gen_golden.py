@@ -39,6 +39,14 @@ def primitives():
     y[:4] = [0, -5, 0, 5]; x[:4] = [0, 0, -3, 5]
     d["atan_y"] = y; d["atan_x"] = x
     d["atan"] = np.array([cv2.fastAtan2(float(a), float(b)) for a, b in zip(y, x)], np.float32)
+    # cv::undistortPoints(pts, pts, K, dist, Mat(), K) as Frame::UndistortKeyPoints calls it (Frame.cc:307)
+    pts = np.stack([rng.uniform(0, 1280, 600), rng.uniform(0, 720, 600)], 1).astype(np.float32)
+    d["und_pts"] = pts
+    for name, K4, dist in [("a", (863.94, 865.22, 642.61, 356.83), (-0.3716, 0.2156, 0.0011, -0.0015)),
+                           ("b", (500., 510., 320., 240.), (0.12, -0.25, 0.001, 0.0005, 0.05))]:
+        K = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]], np.float32)
+        d["und_K_" + name] = np.array(K4, np.float32); d["und_D_" + name] = np.array(dist, np.float32)
+        d["und_out_" + name] = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, np.array(dist, np.float32), None, K).reshape(-1, 2)
     np.savez_compressed(os.path.join(OUT, "primitives.npz"), **d)
 
 

@@ -68,6 +68,7 @@ class Oracle:
             L.orc_hamming_knn2_mt.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _i]
             L.orc_hamming_window.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
             L.orc_search_for_initialization.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp]
+            L.orc_undistort.argtypes = [_vp, _i, _vp, _vp, _i, _i, _vp]
             L.orc_features_in_area.argtypes = [_vp, _vp, _i, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i]
             L.orc_search_by_projection_frame.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
             L.orc_search_by_projection_points.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp]
@@ -191,6 +192,14 @@ class Oracle:
         n = cls.lib().orc_search_for_initialization(_p(D1), len(D1), _p(D2), len(D2), _p(ptr), _p(cand), nnratio,
                                                      None if a1 is None else _p(a1), None if a2 is None else _p(a2), _p(m))
         return n, m
+
+    @classmethod
+    def undistort(cls, xy, K4, dist, mode):
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+        K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist if dist is not None else [], np.float32)
+        out = np.zeros_like(xy)
+        cls.lib().orc_undistort(_p(xy), len(xy), _p(K4), _p(dist) if len(dist) else None, len(dist), mode, _p(out))
+        return out
 
     @classmethod
     def features_in_area(cls, xy, octave, bounds, qx, qy, qr, min_level=None, max_level=None):

@@ -41,6 +41,8 @@ SYMBOLS = [
     ("os1_search_by_projection_frame", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, C.POINTER(_i), _i]),
     ("os1_search_by_projection_points", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp, C.POINTER(_i), _i]),
     ("os1_features_in_area", _i, [_vp, _i, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp]),
+    ("os1_undistort_keypoints", _i, [_vp, _i, _vp, _vp, _i, _i, _vp, _i, _i, _vp]),
+    ("os1_image_bounds", _i, [_i, _i, _vp, _vp, _i, _i, _vp, _i]),
     ("os1_hamming_window", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
 ]
 

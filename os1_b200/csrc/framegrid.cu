@@ -10,6 +10,7 @@
 #include "../../include/os1_b200.h"
 #include "os1_internal.cuh"
 #include <algorithm>
+#include <cstring>
 #include <vector>
 
 #define GRID_COLS 64        // FRAME_GRID_COLS  include/Frame.h:37
@@ -221,4 +222,102 @@ extern "C" int os1_features_in_area(const os1_keypoint* kp, int n, float min_x, 
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_features_in_area: CUDA failure"); return OS1_E_CUDA; }
     return rc;
+}
+
+// ---- Frame::UndistortKeyPoints (src/Frame.cc:286-320) ------------------------------------------------------------------------
+// mode 0: cv::undistortPoints(pts, pts, K, dist, Mat(), K) — five fixed-point iterations of the inverse Brown model in double
+// (the library is compiled with -fmad=false, so every product and sum rounds as the x86 build of OpenCV rounds it);
+// mode 1: os1's equidistant fisheye, antidistorsionarProyeccionEquidistante (:355-384).
+namespace {
+
+struct CamParams { double fx, fy, cx, cy; double k[14]; float Kf[9]; int mode; };
+
+__global__ void undistort_kernel(const os1_kp_dev* in, int n, CamParams C, os1_kp_dev* out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    os1_kp_dev kp = in[i];
+    if (C.mode == 0) {
+        const double ifx = 1. / C.fx, ify = 1. / C.fy;
+        double x = kp.x, y = kp.y;
+        x = (x - C.cx) * ifx; y = (y - C.cy) * ify;
+        const double x0 = x, y0 = y;
+        const double* k = C.k;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = x0; y = y0; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = C.fx * x + 0.0 * y + C.cx, yy = 0.0 * x + C.fy * y + C.cy, ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        kp.x = (float)(xx * ww); kp.y = (float)(yy * ww);
+    } else {
+        const double pwx = ((double)kp.x - C.cx) / C.fx, pwy = ((double)kp.y - C.cy) / C.fy;
+        const double theta_d = sqrt(pwx * pwx + pwy * pwy);
+        const double scale = theta_d > 1e-8 ? tan(theta_d) / theta_d : 1.0;
+        const double pux = pwx * scale, puy = pwy * scale;
+        const double pr0 = C.Kf[0] * pux + C.Kf[1] * puy + C.Kf[2] * 1.0, pr1 = C.Kf[3] * pux + C.Kf[4] * puy + C.Kf[5] * 1.0;
+        const double pr2 = C.Kf[6] * pux + C.Kf[7] * puy + C.Kf[8] * 1.0;
+        kp.x = (float)(pr0 / pr2); kp.y = (float)(pr1 / pr2);
+    }
+    out[i] = kp;
+}
+
+} // namespace
+
+extern "C" int os1_undistort_keypoints(const os1_keypoint* kp, int n, const float* K4, const float* dist, int ndist, int mode, os1_keypoint* kp_un,
+                                       int on_device, int device, void* cuda_stream)
+{
+    if (n < 0 || !K4 || (n > 0 && (!kp || !kp_un)) || ndist < 0 || ndist > 14 || (ndist > 0 && !dist) || (mode != 0 && mode != 1)) {
+        os1_internal_set_error("os1_undistort_keypoints: bad argument");
+        return OS1_E_INVALID;
+    }
+    if (n == 0) return OS1_OK;
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_undistort_keypoints: cudaSetDevice failed (no CPU fallback)"); return OS1_E_CUDA; }
+    const bool identity = mode == 0 && (ndist == 0 || dist[0] == 0.0f);        // Frame.cc:288-292
+    CamParams C;
+    C.fx = K4[0]; C.fy = K4[1]; C.cx = K4[2]; C.cy = K4[3]; C.mode = mode;
+    for (int i = 0; i < 14; i++) C.k[i] = i < ndist ? (double)dist[i] : 0.0;
+    const float Kf[9] = { K4[0], 0.f, K4[2], 0.f, K4[1], K4[3], 0.f, 0.f, 1.f };
+    for (int i = 0; i < 9; i++) C.Kf[i] = Kf[i];
+    const size_t bytes = (size_t)n * sizeof(os1_kp_dev);
+    if (on_device) {
+        if (identity) e = kp == kp_un ? cudaSuccess : cudaMemcpyAsync(kp_un, kp, bytes, cudaMemcpyDeviceToDevice, s);
+        else { undistort_kernel<<<(n + 127) / 128, 128, 0, s>>>((const os1_kp_dev*)kp, n, C, (os1_kp_dev*)kp_un); e = cudaGetLastError(); }
+        if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_undistort_keypoints: CUDA failure"); return OS1_E_CUDA; }
+        return OS1_OK;
+    }
+    if (identity) { if (kp != kp_un) memcpy(kp_un, kp, bytes); return OS1_OK; }
+    os1_kp_dev* d = nullptr;
+    e = cudaMallocAsync((void**)&d, bytes, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d, kp, bytes, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) { undistort_kernel<<<(n + 127) / 128, 128, 0, s>>>(d, n, C, d); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(kp_un, d, bytes, cudaMemcpyDeviceToHost, s);
+    if (d) cudaFreeAsync(d, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_undistort_keypoints: CUDA failure"); return OS1_E_CUDA; }
+    return OS1_OK;
+}
+
+// Frame::ComputeImageBounds (src/Frame.cc:322-353): the four image corners through the same undistortion
+extern "C" int os1_image_bounds(int cols, int rows, const float* K4, const float* dist, int ndist, int mode, float* bounds4, int device)
+{
+    if (!bounds4 || !K4 || cols <= 0 || rows <= 0) { os1_internal_set_error("os1_image_bounds: bad argument"); return OS1_E_INVALID; }
+    if (mode == 0 && (ndist == 0 || dist[0] == 0.0f)) {
+        bounds4[0] = 0.0f; bounds4[1] = (float)cols; bounds4[2] = 0.0f; bounds4[3] = (float)rows;
+        return OS1_OK;
+    }
+    os1_keypoint c[4];
+    memset(c, 0, sizeof(c));
+    c[0].x = 0.0f; c[0].y = 0.0f; c[1].x = (float)cols; c[1].y = 0.0f; c[2].x = 0.0f; c[2].y = (float)rows; c[3].x = (float)cols; c[3].y = (float)rows;
+    const int rc = os1_undistort_keypoints(c, 4, K4, dist, ndist, mode, c, 0, device, nullptr);
+    if (rc) return rc;
+    bounds4[0] = std::min(c[0].x, c[2].x); bounds4[1] = std::max(c[1].x, c[3].x);       // mnMinX, mnMaxX
+    bounds4[2] = std::min(c[0].y, c[1].y); bounds4[3] = std::max(c[2].y, c[3].y);       // mnMinY, mnMaxY
+    return OS1_OK;
 }

@@ -137,3 +137,23 @@ def GetFeaturesInArea(kp, bounds, qx, qy, qr, min_level=None, max_level=None, de
             continue
         _lib.check(rc)
         return ptr, cand[:ptr[nq]].copy()
+
+
+def UndistortKeyPoints(kp, K4, dist=None, mode=0, device=0):
+    """Frame::UndistortKeyPoints (Frame.cc:286-320): mode 0 pinhole (cv::undistortPoints), mode 1 os1's equidistant fisheye."""
+    kp = np.ascontiguousarray(kp)
+    out = np.zeros_like(kp)
+    K4 = np.ascontiguousarray(K4, np.float32)
+    d = np.ascontiguousarray(dist if dist is not None else [], np.float32)
+    _lib.check(_lib.load().os1_undistort_keypoints(_ptr(kp), len(kp), _ptr(K4), _ptr(d) if len(d) else None, len(d), mode, _ptr(out), 0,
+                                                    device, None))
+    return out
+
+
+def ComputeImageBounds(cols, rows, K4, dist=None, mode=0, device=0):
+    """Frame::ComputeImageBounds (Frame.cc:322-353) -> (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    K4 = np.ascontiguousarray(K4, np.float32)
+    d = np.ascontiguousarray(dist if dist is not None else [], np.float32)
+    b = np.zeros(4, np.float32)
+    _lib.check(_lib.load().os1_image_bounds(cols, rows, _ptr(K4), _ptr(d) if len(d) else None, len(d), mode, _ptr(b), device))
+    return tuple(float(v) for v in b)

@@ -73,3 +73,45 @@ def test_grid_to_matcher_pipeline(oracle_lib, frame_kp):
     n, m = matcher.SearchForInitialization(d0, d1, ptr, cand, 0.9, k0["angle"], k1["angle"])
     rn, rm = oracle_lib.Oracle.search_for_initialization(d0, d1, ptr, cand, 0.9, k0["angle"], k1["angle"])
     assert n == rn and np.array_equal(m, rm[:len(m)]) and n > 100
+
+
+# ---- Frame::UndistortKeyPoints / ComputeImageBounds --------------------------------------------------------------------------
+SONY_720P = ((863.94, 865.22, 642.61, 356.83), (-0.3716, 0.2156, 0.0011, -0.0015))       # a pinhole calibration with k1,k2,p1,p2
+
+
+@pytest.mark.parametrize("K4,dist", [SONY_720P, ((500., 510., 320., 240.), (0.12, -0.25, 0.001, 0.0005, 0.05)),
+                                     ((700., 700., 640., 360.), (-0.2, 0.05, 0, 0, 0, 0.01, 0.02, 0.003))])
+def test_undistort_pinhole_bit_exact(oracle_lib, frame_kp, K4, dist):
+    k, _ = frame_kp
+    un = matcher.UndistortKeyPoints(k, K4, dist, 0)
+    ref = oracle_lib.Oracle.undistort(np.stack([k["x"], k["y"]], 1), K4, dist, 0)      # pinned to cv2.undistortPoints on the CPU side
+    assert np.array_equal(un["x"], ref[:, 0]) and np.array_equal(un["y"], ref[:, 1])
+    for f in ("size", "angle", "response", "octave", "class_id"):
+        assert np.array_equal(un[f], k[f])
+    cv2 = pytest.importorskip("cv2")
+    K = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]], np.float32)
+    r2 = cv2.undistortPoints(np.stack([k["x"], k["y"]], 1).reshape(-1, 1, 2), K, np.array(dist, np.float32), None, K).reshape(-1, 2)
+    assert np.array_equal(un["x"], r2[:, 0]) and np.array_equal(un["y"], r2[:, 1])
+
+
+def test_undistort_identity_and_fisheye(oracle_lib, frame_kp):
+    k, _ = frame_kp
+    same = matcher.UndistortKeyPoints(k, (700., 700., 640., 360.), (0.0, 0.1, 0, 0), 0)       # dist[0] == 0 -> mvKeysUn = mvKeys
+    assert np.array_equal(same, k)
+    K4 = (520.0, 520.0, 640.0, 360.0)
+    un = matcher.UndistortKeyPoints(k, K4, None, 1)
+    ref = oracle_lib.Oracle.undistort(np.stack([k["x"], k["y"]], 1), K4, None, 1)
+    # double-precision tan() on the GPU vs glibc: results may differ in the last float bit
+    assert np.abs(un["x"] - ref[:, 0]).max() <= 1e-3 and np.abs(un["y"] - ref[:, 1]).max() <= 1e-3
+    assert ((un["x"] == ref[:, 0]) & (un["y"] == ref[:, 1])).mean() > 0.99
+    # the fisheye model pushes points outwards: |un - c| >= |kp - c|
+    assert (np.hypot(un["x"] - 640, un["y"] - 360) >= np.hypot(k["x"] - 640, k["y"] - 360) - 1e-3).all()
+
+
+def test_image_bounds(oracle_lib):
+    K4, dist = SONY_720P
+    b = matcher.ComputeImageBounds(1280, 720, K4, dist, 0)
+    c = oracle_lib.Oracle.undistort(np.array([[0, 0], [1280, 0], [0, 720], [1280, 720]], np.float32), K4, dist, 0)
+    ref = (min(c[0, 0], c[2, 0]), max(c[1, 0], c[3, 0]), min(c[0, 1], c[1, 1]), max(c[2, 1], c[3, 1]))
+    assert b == tuple(float(v) for v in ref)
+    assert matcher.ComputeImageBounds(640, 480, K4, (0.0,), 0) == (0.0, 640.0, 0.0, 480.0)

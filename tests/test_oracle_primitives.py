@@ -54,3 +54,12 @@ def test_primitives_against_live_cv2(oracle_lib):
 def test_fast_small_and_flat_images(oracle_lib):
     assert len(oracle_lib.Oracle.fast(np.zeros((6, 40), np.uint8), 7)) == 0          # fewer than 7 rows: nothing is tested
     assert len(oracle_lib.Oracle.fast(np.full((40, 40), 128, np.uint8), 7)) == 0
+
+
+def test_undistort_points_bit_exact(oracle_lib, gold):
+    """Frame::UndistortKeyPoints' pinhole branch = cv::undistortPoints with P = K (Frame.cc:307)."""
+    for name in ("a", "b"):
+        out = oracle_lib.Oracle.undistort(gold["und_pts"], gold["und_K_" + name], gold["und_D_" + name], 0)
+        assert np.array_equal(out, gold["und_out_" + name])
+    same = oracle_lib.Oracle.undistort(gold["und_pts"], gold["und_K_a"], [0.0, 0.3, 0, 0], 0)
+    assert np.array_equal(same, gold["und_pts"])          # dist[0] == 0 -> identity (Frame.cc:288-292)
