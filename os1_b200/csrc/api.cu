@@ -258,7 +258,7 @@ int build_geometry(os1_orb* h, int rows, int cols)
     if (h->planBig) os1_pyramid_plan_destroy(h->planBig);
     h->planBig = nullptr;
     {
-        // coarsest-level tile: 32x16 keeps a single frame spread over enough CTAs; batches use 48x24 (less halo,
+        // coarsest-level tile: 32x16 keeps a single frame spread over enough CTAs; batches use 40x20 (less halo,
         // fewer block-wide phases).  A tile whose level-0 footprint exceeds a TMA box (256) falls back to a smaller one.
         const int cand[][2] = { { 32, 16 }, { 24, 12 }, { 16, 8 }, { 8, 8 } };
         for (auto& c : cand) {
@@ -267,7 +267,7 @@ int build_geometry(os1_orb* h, int rows, int cols)
             os1_pyramid_plan_destroy(h->plan); h->plan = nullptr;
         }
         if (!h->plan) return fail(h, OS1_E_UNSUPPORTED, "no pyramid tile fits a TMA box for this scale factor / level count");
-        int tw = 48, th = 24;
+        int tw = 40, th = 20;
         if (const char* e = getenv("OS1_PYR_TILE")) sscanf(e, "%dx%d", &tw, &th);
         h->planBig = os1_pyramid_plan_create(g, tw, th);
         if (!os1_pyramid_plan_ok(h->planBig)) { os1_pyramid_plan_destroy(h->planBig); h->planBig = nullptr; }
