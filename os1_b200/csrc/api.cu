@@ -44,6 +44,8 @@ struct os1_orb {
     int device;
     cudaStream_t ownStream = nullptr, stream = nullptr;
     cudaStream_t inStream = nullptr, outStream = nullptr;       // upload / download streams of the chunked host path
+    cudaStream_t altStream = nullptr;                           // second compute stream: odd chunks, so one chunk's tail waves overlap the next
+    cudaEvent_t altEv = nullptr;
     std::vector<cudaEvent_t> chunkEv;                           // 2 per chunk: uploaded, computed
     std::string err;
 
@@ -331,8 +333,9 @@ int check_status(os1_orb* h, int st)
 // the four launches of one extraction over `nframes` frames whose level 0 is already on the device
 // (frames [f0, f0+nframes) of the handle's per-frame buffers; kp/desc/counts are already offset by the caller)
 int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0Pitch, int nframes, os1_kp_dev* kp, uint8_t* desc,
-                 int cap, int* counts, int f0 = 0)
+                 int cap, int* counts, int f0 = 0, cudaStream_t st = nullptr)
 {
+    if (!st) st = h->stream;
     const Geometry& g = h->geom;
     DevPtrs d;
     const long long F = f0;
@@ -348,15 +351,15 @@ int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0
     if (f0 == 0) { h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch; }
     h->lastFrames = f0 + nframes;
     const bool t = h->timing && f0 == 0;
-    if (t) CK(cudaEventRecord(h->ev[0], h->stream), "cudaEventRecord");
-    CK(os1_launch_pyramid((nframes >= 4 && h->planBig) ? h->planBig : h->plan, g, d, nframes, h->stream), "pyramid kernel");
-    if (t) CK(cudaEventRecord(h->ev[1], h->stream), "cudaEventRecord");
-    CK(os1_launch_fast(g, d, nframes, h->stream), "FAST kernel");
-    if (t) CK(cudaEventRecord(h->ev[2], h->stream), "cudaEventRecord");
-    CK(os1_launch_quadtree(g, d, nframes, h->maxQuota, h->maxCells, h->stream), "quadtree kernel");
-    if (t) CK(cudaEventRecord(h->ev[3], h->stream), "cudaEventRecord");
-    CK(os1_launch_describe(g, d, nframes, kp, desc, cap, counts, h->stream), "describe kernel");
-    if (t) CK(cudaEventRecord(h->ev[4], h->stream), "cudaEventRecord");
+    if (t) CK(cudaEventRecord(h->ev[0], st), "cudaEventRecord");
+    CK(os1_launch_pyramid((nframes >= 4 && h->planBig) ? h->planBig : h->plan, g, d, nframes, st), "pyramid kernel");
+    if (t) CK(cudaEventRecord(h->ev[1], st), "cudaEventRecord");
+    CK(os1_launch_fast(g, d, nframes, st), "FAST kernel");
+    if (t) CK(cudaEventRecord(h->ev[2], st), "cudaEventRecord");
+    CK(os1_launch_quadtree(g, d, nframes, h->maxQuota, h->maxCells, st), "quadtree kernel");
+    if (t) CK(cudaEventRecord(h->ev[3], st), "cudaEventRecord");
+    CK(os1_launch_describe(g, d, nframes, kp, desc, cap, counts, st), "describe kernel");
+    if (t) CK(cudaEventRecord(h->ev[4], st), "cudaEventRecord");
     return OS1_OK;
 }
 
@@ -414,6 +417,8 @@ int os1_orb_destroy(os1_orb* h)
     if (h->hostStatus) cudaFreeHost(h->hostStatus);
     for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (cudaEvent_t e : h->chunkEv) cudaEventDestroy(e);
+    if (h->altStream) cudaStreamDestroy(h->altStream);
+    if (h->altEv) cudaEventDestroy(h->altEv);
     if (h->inStream) cudaStreamDestroy(h->inStream);
     if (h->outStream) cudaStreamDestroy(h->outStream);
     if (h->ownStream) cudaStreamDestroy(h->ownStream);
@@ -587,13 +592,17 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     // copies of neighbouring chunks hide behind the kernels of the current one ----------------------------------------------
     int chunk = 64;
     if (const char* e = getenv("OS1_CHUNK")) chunk = std::max(1, atoi(e));
-    // chunk boundaries: the first two chunks are a quarter and a half of the steady size, so the kernels start after a
-    // short upload instead of idling through a full one
+    // chunk boundaries: a geometric ramp.  The upload of chunk c+1 hides behind the kernels of chunk c only while it is
+    // not longer than them, so chunks grow by less than the kernel-time / upload-time ratio per frame (1.31 at 720p over
+    // PCIe 5 x16); the kernels then start after the upload of a few frames and never starve again
+    int ramp0 = std::max(1, chunk / 8), rampPct = 125;
+    if (const char* e = getenv("OS1_RAMP0")) ramp0 = std::max(1, atoi(e));
+    if (const char* e = getenv("OS1_RAMPPCT")) rampPct = std::max(100, atoi(e));
     std::vector<int> cuts(1, 0);
-    for (int f = 0, c = 0; f < nframes; c++) {
-        const int sz = std::max(1, c == 0 ? chunk / 4 : (c == 1 ? chunk / 2 : chunk));
+    for (int f = 0, sz = std::min(ramp0, chunk); f < nframes;) {
         f = std::min(nframes, f + sz);
         cuts.push_back(f);
+        sz = std::min(chunk, std::max(sz + 1, sz * rampPct / 100));
     }
     const int nchunks = (int)cuts.size() - 1;
     if (!h->inStream) CK(cudaStreamCreateWithFlags(&h->inStream, cudaStreamNonBlocking), "cudaStreamCreate");
@@ -607,21 +616,31 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     CK(cudaEventRecord(h->chunkEv[2 * nchunks], h->stream), "cudaEventRecord");
     CK(cudaStreamWaitEvent(h->inStream, h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
     CK(cudaStreamWaitEvent(h->outStream, h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
+    // odd chunks run on a second compute stream (their scratch is disjoint): the partial last waves of one chunk's
+    // kernels are filled by the other chunk's
+    static const bool useAlt = !(getenv("OS1_ALT") && atoi(getenv("OS1_ALT")) == 0);
+    const bool alt = useAlt && nchunks > 1;
+    if (alt) {
+        if (!h->altStream) CK(cudaStreamCreateWithFlags(&h->altStream, cudaStreamNonBlocking), "cudaStreamCreate");
+        if (!h->altEv) CK(cudaEventCreateWithFlags(&h->altEv, cudaEventDisableTiming), "cudaEventCreate");
+        CK(cudaStreamWaitEvent(h->altStream, h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
+    }
     const size_t kpRow = (size_t)dCap * sizeof(os1_kp_dev), dRow = (size_t)dCap * 32;
     const int copyCap = std::min(dCap, cap_per_frame);
     for (int c = 0; c < nchunks; c++) {
         const int f0 = cuts[c], n = cuts[c + 1] - cuts[c];
+        cudaStream_t cs = (alt && (c & 1)) ? h->altStream : h->stream;
         if (!direct) {
-            CK(stage_in(f0, n, frames_on_device ? h->stream : h->inStream), "upload frames");
+            CK(stage_in(f0, n, frames_on_device ? cs : h->inStream), "upload frames");
             if (!frames_on_device) {
                 CK(cudaEventRecord(h->chunkEv[2 * c], h->inStream), "cudaEventRecord");
-                CK(cudaStreamWaitEvent(h->stream, h->chunkEv[2 * c], 0), "cudaStreamWaitEvent");
+                CK(cudaStreamWaitEvent(cs, h->chunkEv[2 * c], 0), "cudaStreamWaitEvent");
             }
         }
-        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, n, dKp + (size_t)f0 * dCap, dDesc + (size_t)f0 * dRow, dCap, dCnt + f0, f0);
+        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, n, dKp + (size_t)f0 * dCap, dDesc + (size_t)f0 * dRow, dCap, dCnt + f0, f0, cs);
         if (rc) return rc;
         if (!out_on_device) {
-            CK(cudaEventRecord(h->chunkEv[2 * c + 1], h->stream), "cudaEventRecord");
+            CK(cudaEventRecord(h->chunkEv[2 * c + 1], cs), "cudaEventRecord");
             CK(cudaStreamWaitEvent(h->outStream, h->chunkEv[2 * c + 1], 0), "cudaStreamWaitEvent");
             // straight into the caller's slabs (row = frame; pitches differ when the caller's capacity does)
             CK(cudaMemcpy2DAsync(kp + (size_t)f0 * cap_per_frame, (size_t)cap_per_frame * sizeof(os1_keypoint), dKp + (size_t)f0 * dCap, kpRow,
@@ -630,6 +649,10 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
                                  (size_t)copyCap * 32, n, cudaMemcpyDeviceToHost, h->outStream), "download descriptors");
             CK(cudaMemcpyAsync(counts + f0, dCnt + f0, (size_t)n * 4, cudaMemcpyDeviceToHost, h->outStream), "download counts");
         }
+    }
+    if (alt) {       // join: everything queued on the second stream is ordered before what follows on the handle's stream
+        CK(cudaEventRecord(h->altEv, h->altStream), "cudaEventRecord");
+        CK(cudaStreamWaitEvent(h->stream, h->altEv, 0), "cudaStreamWaitEvent");
     }
     CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
     CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
