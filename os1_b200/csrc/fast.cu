@@ -20,9 +20,12 @@
 //            the response is finished in packed form too (saturating differences as max(a,b)-b, no cross-lane
 //            borrow) and stored as max(strength - tmin, 0): zero below min(iniTh, minTh), which leaves NMS
 //            unchanged and makes the maps sparse;
-//   phase 3  NMS on the packed maps (native VIMNMX3.U16x2), skipping empty groups; cell boundaries are lane masks;
-//            the few survivors are appended to a per-cell list in shared memory;
-//   phase 4  per cell: vote "any survivor >= iniTh", rank every survivor by (row, column) by counting, emit.
+//   phase 3  NMS as a column sweep: a thread owns one group of four columns and walks down a band of rows with the
+//            horizontal neighbour maxima of three rows in registers (4 word loads + ~25 ALU instructions per row,
+//            no divergence); cell boundaries are lane masks; survivors become bits of a per-row bitmap of the tile;
+//   phase 4  one warp per cell, one lane per row: cut the cell's columns out of the row bitmaps, vote "any survivor
+//            >= iniTh", take the exclusive prefix of the per-row counts and emit row by row, left to right — which is
+//            cv::FAST's output order, so nothing is ever sorted.
 #include "os1_internal.cuh"
 
 #define FAST_THREADS 256
@@ -34,7 +37,7 @@ struct FastParams {
     DevPtrs d;
     int pitchW;         // shared-memory row pitch in 32-bit words
     int tileRows;
-    int listCap;        // survivor slots per cell in shared memory
+    int bmWords;        // words per row of the survivor bitmap (one bit per tile byte column, + 2 spare)
 };
 
 // ---- packed ring access -------------------------------------------------------------------------------------
@@ -102,7 +105,7 @@ __device__ __forceinline__ void arc_extremes(const unsigned (&W)[7][3], unsigned
 __device__ __forceinline__ unsigned usubsat2(unsigned a, unsigned b) { return __vmaxu2(a, b) - b; }     // max(a-b, 0)
 
 template <int PW>
-__global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constant__ FastParams P)
+__global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_constant__ FastParams P)
 {
     extern __shared__ __align__(16) unsigned smw[];
     const Geometry& g = P.g;
@@ -132,11 +135,8 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constan
     unsigned* lmO = lmE + pw;
     unsigned* rmE = lmO + pw;                    // 0 in the lane whose pixel is a cell's LAST tested column
     unsigned* rmO = rmE + pw;
-    unsigned* lists = rmO + pw;                  // [FAST_G][listCap]: survivors >= iniTh grow from the front of a cell's
-                                                 // slots, the weaker ones from the back (together <= the NMS bound)
-    unsigned char* cellOf = (unsigned char*)(lists + FAST_G * P.listCap);   // cell index of every tile byte column
-    __shared__ int s_n[2][FAST_G];
-    const int listCap = P.listCap;
+    unsigned* bm = rmO + pw;                     // [tileRows][bmWords]: bit c of a row <-> tile byte column c survived the NMS
+    const int bw = P.bmWords;
     const int xorg = (x0 & ~3) - 4;             // global x of tile byte 0 (one spare word on the left)
     const int words = ((x1 + 3 - xorg) >> 2) + 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -156,17 +156,16 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constan
     const int tr0 = 3, tr1 = th - 3;                          // tested rows
     const int wCell = L.wCell;
 
-    // ---- phase 0/1: lane masks, tile -> shared, cleared score maps --------------------------------------------------
-    if (tid < 2 * FAST_G) s_n[tid / FAST_G][tid % FAST_G] = 0;
+    // ---- phase 0/1: lane masks, tile -> shared, cleared score-map frame and bitmap ------------------------------------
+    const unsigned rcpW = 65536u / (unsigned)wCell + 1u;     // rel / wCell == (rel * rcpW) >> 16 while rel * wCell < 2^16
     for (int w = tid; w < pw; w += FAST_THREADS) {
         unsigned vm[4], lm[4], rm[4];
 #pragma unroll
         for (int b = 0; b < 4; b++) {
             const int col = 4 * w + b;
             const bool in = col >= tc0 && col < tc1;
-            const int rel = col - tc0;
-            const int q = in ? rel % wCell : 1;
-            cellOf[col] = (unsigned char)(in ? rel / wCell : 0);
+            const int rel = in ? col - tc0 : 1;
+            const int q = rel - (int)(((unsigned)rel * rcpW) >> 16) * wCell;       // rel % wCell
             vm[b] = in ? 0xFFFFu : 0u;
             lm[b] = (in && q == 0) ? 0u : 0xFFFFu;
             rm[b] = (in && (q == wCell - 1 || col == tc1 - 1)) ? 0u : 0xFFFFu;
@@ -175,6 +174,7 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constan
         lmE[w] = lm[0] | (lm[2] << 16); lmO[w] = lm[1] | (lm[3] << 16);
         rmE[w] = rm[0] | (rm[2] << 16); rmO[w] = rm[1] | (rm[3] << 16);
     }
+    for (int i = tid; i < th * bw; i += FAST_THREADS) bm[i] = 0;
     const int g0 = tc0 >> 2, g1 = (tc1 + 3) >> 2;
     // tile: asynchronous 4-byte copies straight into shared memory (LDGSTS), all in flight at once
     for (int r = warp; r < th; r += FAST_THREADS / 32) {
@@ -226,80 +226,119 @@ __global__ void __launch_bounds__(FAST_THREADS) fast_kernel(const __grid_constan
     }
     __syncthreads();
 
-    // ---- phase 3: NMS on the packed maps; survivors go to their cell's list ----------------------------------------------
-    for (int idx = tid; idx < nItems; idx += FAST_THREADS) {
-            const int rr = (int)(((unsigned)idx * rcpNg) >> 24);
-            const int r = tr0 + rr, gq = g0 + idx - rr * ng;
-            const int o = r * pw + gq;
-            const unsigned vE = scE[o], vO = scO[o];
-            if ((vE | vO) == 0) continue;
-            unsigned keepE = 0, keepO = 0;          // lanes that beat all eight neighbours
+    // ---- phase 3: NMS sweep.  Thread = (group of four columns, band of rows).  For a row, H3 = max(left, centre, right)
+    // and H2 = max(left, right) of the two pixel pairs (E = pixels 0,2; O = pixels 1,3), with the neighbours that lie in
+    // another cell masked out; a pixel survives when it beats H3 of the rows above and below and H2 of its own row. -----
+    {
+        const int nr = tr1 - tr0;
+        const int nb = max(1, min(FAST_THREADS / ng, nr));                  // bands of rows
+        const int rpb = (nr + nb - 1) / nb;
+        const int band = (int)(((unsigned)tid * rcpNg) >> 24);
+        const int gq = g0 + tid - band * ng;
+        const int rb = tr0 + band * rpb, re = min(tr1, rb + rpb);
+        if (band < nb && rb < re) {
+            const unsigned lE = lmE[gq], rE = rmE[gq], lO = lmO[gq], rO = rmO[gq];
+            const unsigned ONES = 0x00010001u;
+            const int sh = 4 * (gq & 7);
+            unsigned* bmw = bm + (gq >> 3);
+            unsigned h3Ep, h3Op, h2Ec, h3Ec, h2Oc, h3Oc, ec, oc;
+            // horizontal maxima of one row
+            auto hrow = [&](int r, unsigned& e, unsigned& o, unsigned& h2E, unsigned& h3E, unsigned& h2O, unsigned& h3O) {
+                const unsigned* q = scE + r * pw + gq;
+                const unsigned* t = scO + r * pw + gq;
+                e = q[0]; o = t[0];
+                const unsigned leftE = __byte_perm(t[-1], o, 0x5432) & lE;       // pixels -1, 1
+                const unsigned rightE = o & rE;                                  // pixels  1, 3
+                const unsigned leftO = e & lO;                                   // pixels  0, 2
+                const unsigned rightO = __byte_perm(e, q[1], 0x5432) & rO;       // pixels  2, 4
+                h2E = __vmaxu2(leftE, rightE); h3E = __vimax3_u16x2(leftE, e, rightE);
+                h2O = __vmaxu2(leftO, rightO); h3O = __vimax3_u16x2(leftO, o, rightO);
+            };
             {
-                // even pixels (0,2): left neighbours = (odd[-1].hi, odd.lo), right neighbours = odd
-                const unsigned lm = lmE[gq], rm = rmE[gq];
-                unsigned m = __vimax3_u16x2(__byte_perm(scO[o - pw - 1], scO[o - pw], 0x5432) & lm, scE[o - pw], scO[o - pw] & rm);
-                m = __vimax3_u16x2(m, __byte_perm(scO[o + pw - 1], scO[o + pw], 0x5432) & lm, scE[o + pw]);
-                m = __vimax3_u16x2(m, scO[o + pw] & rm, __byte_perm(scO[o - 1], vO, 0x5432) & lm);
-                m = __vmaxu2(m, vO & rm);
-                if ((vE & 0xFFFFu) > (m & 0xFFFFu)) keepE |= 1;
-                if ((vE >> 16) > (m >> 16)) keepE |= 2;
+                unsigned e, o, h2E, h2O;
+                hrow(rb - 1, e, o, h2E, h3Ep, h2O, h3Op);
             }
-            {
-                // odd pixels (1,3): left neighbours = even, right neighbours = (even.hi, even[+1].lo)
-                const unsigned lm = lmO[gq], rm = rmO[gq];
-                unsigned m = __vimax3_u16x2(scE[o - pw] & lm, scO[o - pw], __byte_perm(scE[o - pw], scE[o - pw + 1], 0x5432) & rm);
-                m = __vimax3_u16x2(m, scE[o + pw] & lm, scO[o + pw]);
-                m = __vimax3_u16x2(m, __byte_perm(scE[o + pw], scE[o + pw + 1], 0x5432) & rm, vE & lm);
-                m = __vmaxu2(m, __byte_perm(vE, scE[o + 1], 0x5432) & rm);
-                if ((vO & 0xFFFFu) > (m & 0xFFFFu)) keepO |= 1;
-                if ((vO >> 16) > (m >> 16)) keepO |= 2;
-            }
-            // bit b of `kept` <-> pixel b of the group; survivors are few, so this loop rarely runs
-            unsigned kept = (keepE & 1) | ((keepO & 1) << 1) | ((keepE & 2) << 1) | ((keepO & 2) << 2);
-            while (kept) {
-                const int b = __ffs(kept) - 1;
-                kept &= kept - 1;
-                const unsigned v = (b & 1) ? vO : vE;
-                const int s8 = ((b >> 1) ? (v >> 24) : (v >> 8)) & 0xFF;       // strength - tmin  (>= 1)
-                const int col = 4 * gq + b;
-                const int cc = cellOf[col];
-                const int which = s8 >= iniS8 ? 0 : 1;
-                const int slot = atomicAdd(&s_n[which][cc], 1);
-                if (slot < listCap) lists[cc * listCap + (which ? listCap - 1 - slot : slot)] = ((unsigned)r << 22) | ((unsigned)col << 8) | (unsigned)s8;
+            hrow(rb, ec, oc, h2Ec, h3Ec, h2Oc, h3Oc);
+#pragma unroll 2
+            for (int r = rb; r < re; r++) {
+                unsigned en, on, h2En, h3En, h2On, h3On;
+                hrow(r + 1, en, on, h2En, h3En, h2On, h3On);
+                const unsigned mE = __vimax3_u16x2(h3Ep, h2Ec, h3En), mO = __vimax3_u16x2(h3Op, h2Oc, h3On);
+                // lanes that beat all eight neighbours -> 1 (a non-zero difference of two multiples of 257 is >= 257)
+                const unsigned nE = __vminu2(__vmaxu2(ec, mE) - mE, ONES), nO = __vminu2(__vmaxu2(oc, mO) - mO, ONES);
+                const unsigned x = 2u * nO + nE;                                  // bits 0,1 <-> pixels 0,1; bits 16,17 <-> pixels 2,3
+                const unsigned nib = (x | (x >> 14)) & 0xFu;
+                if (nib) atomicOr(bmw + r * bw, nib << sh);
+                h3Ep = h3Ec; h3Op = h3Oc;
+                h2Ec = h2En; h3Ec = h3En; h2Oc = h2On; h3Oc = h3On; ec = en; oc = on;
             }
         }
+    }
     __syncthreads();
 
-    // ---- phase 4: per cell — the >= iniTh list if it is not empty, else the weaker one (the reference's retry with
-    // minThFAST, ORBextractor.cc:852-856); rank by (row, column) by counting; emit in cv::FAST's order -----------------
-    for (int cc = warp; cc < ncell; cc += FAST_THREADS / 32) {          // one warp per cell, lanes = survivors
-        const int nA = s_n[0][cc], nB = s_n[1][cc];
-        if (nA + nB > listCap && lane == 0) atomicOr(P.d.status, OS1_ERR_CELL_OVERFLOW);
-        const int which = nA > 0 ? 0 : 1;
-        // with iniTh <= minTh the retry adds nothing: the weaker list is then empty (tmin = iniTh), so the rule above
-        // still reproduces the reference
-        const int n = min(which ? nB : nA, listCap);
-        const unsigned* lst = lists + cc * listCap + (which ? listCap - n : 0);
+    // ---- phase 4: per cell, one lane per row — the survivors >= iniTh if there are any, else those >= minTh (the reference's
+    // retry with minThFAST, ORBextractor.cc:852-856), emitted in row-major order (cv::FAST's) ---------------------------
+    for (int cc = warp; cc < ncell; cc += FAST_THREADS / 32) {
+        const int cx0 = tc0 + cc * wCell, cx1 = min(cx0 + wCell, tc1);      // tile byte columns of the cell (at most 64)
+        const int wsel = cx0 >> 5, bsh = cx0 & 31, width = cx1 - cx0;
+        const unsigned keepLo = width >= 32 ? 0xFFFFFFFFu : ((1u << width) - 1u);
+        const unsigned keepHi = width >= 64 ? 0xFFFFFFFFu : (width > 32 ? ((1u << (width - 32)) - 1u) : 0u);
         uint32_t* out = P.d.stage + (long long)frame * g.candPerFrame + L.candOff + (long long)(ci * L.nCols + j0 + cc) * L.cellCap;
-        const int lim = which ? minS8 : 0;                                 // every entry of the strong list passes
-        int emitted = 0;
-        for (int i0 = 0; i0 < n; i0 += 32) {
-            const int i = i0 + lane;
-            const unsigned e = i < n ? lst[i] : 0u;
-            const bool pass = i < n && (int)(e & 0xFF) >= lim;
-            int rank = 0;
-            for (int j = 0; j < n; j++) {
-                const unsigned f = lst[j];                                  // broadcast read
-                rank += (f < e) && ((int)(f & 0xFF) >= lim);
+        // score byte (strength - tmin) of tile byte column c in row r
+        auto score8 = [&](int r, int c) -> int {
+            const unsigned v = ((c & 1) ? scO : scE)[r * pw + (c >> 2)];
+            return (int)(((c & 2) ? (v >> 24) : (v >> 8)) & 0xFFu);
+        };
+        // the cell's survivors in row r, and which of them reach iniTh / minTh
+        auto classify = [&](int r, unsigned& sLo, unsigned& sHi, unsigned& pLo, unsigned& pHi) {
+            sLo = sHi = pLo = pHi = 0;
+            if (r >= tr1) return;
+            const unsigned* w = bm + r * bw + wsel;
+            const unsigned w0 = w[0], w1 = w[1], w2 = w[2];
+            unsigned a = __funnelshift_r(w0, w1, bsh) & keepLo, b = __funnelshift_r(w1, w2, bsh) & keepHi;
+            while (a | b) {
+                const bool inLo = a != 0;
+                const int bit = inLo ? __ffs(a) - 1 : __ffs(b) - 1;
+                if (inLo) a &= a - 1; else b &= b - 1;
+                const int s8 = score8(r, cx0 + bit + (inLo ? 0 : 32));
+                const unsigned m = 1u << bit;
+                if (s8 >= iniS8) { if (inLo) sLo |= m; else sHi |= m; }
+                if (s8 >= minS8) { if (inLo) pLo |= m; else pHi |= m; }
             }
-            if (pass) {
-                const int r = e >> 22, col = (e >> 8) & 0x3FFF;
-                if (rank < L.cellCap)
-                    out[rank] = OS1_PACK_XYS(col + xorg - OS1_BORDER, r + y0 - OS1_BORDER, (int)(e & 0xFF) + tmin - 1);
-            }
-            emitted += __popc(__ballot_sync(0xffffffffu, pass));
+        };
+        const bool oneTrip = tr1 - tr0 <= 32;             // (cells with more than 32 tested rows take several trips)
+        unsigned sLo, sHi, pLo, pHi;
+        bool st = false;
+        for (int r0 = tr0; r0 < tr1; r0 += 32) {
+            classify(r0 + lane, sLo, sHi, pLo, pHi);
+            st = st || (sLo | sHi) != 0;
         }
-        if (lane == 0) cellCnt[cc] = min(emitted, L.cellCap);
+        const bool strong = __any_sync(0xffffffffu, st);
+        int base = 0;
+        for (int r0 = tr0; r0 < tr1; r0 += 32) {
+            const int r = r0 + lane;
+            if (!oneTrip) classify(r, sLo, sHi, pLo, pHi);       // one trip: the vote's masks are this trip's
+            unsigned mLo = strong ? sLo : pLo, mHi = strong ? sHi : pHi;
+            const int cnt = __popc(mLo) + __popc(mHi);
+            int incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += t;
+            }
+            int rank = base + incl - cnt;
+            base += __shfl_sync(0xffffffffu, incl, 31);
+            while (mLo | mHi) {
+                const bool inLo = mLo != 0;
+                const int bit = inLo ? __ffs(mLo) - 1 : __ffs(mHi) - 1;
+                if (inLo) mLo &= mLo - 1; else mHi &= mHi - 1;
+                const int col = cx0 + bit + (inLo ? 0 : 32);
+                const int s8 = score8(r, col);
+                if (rank < L.cellCap) out[rank] = OS1_PACK_XYS(col + xorg - OS1_BORDER, r + y0 - OS1_BORDER, s8 + tmin - 1);
+                rank++;
+            }
+        }
+        if (lane == 0) cellCnt[cc] = min(base, L.cellCap);
     }
 }
 
@@ -323,19 +362,19 @@ cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cu
     FastParams P;
     P.g = g; P.d = d;
     int maxW = 0, maxH = 0;
-    P.listCap = 1;
     for (int l = 0; l < g.nlevels; l++) {
         if (g.lv[l].nCells == 0) continue;
         maxW = max(maxW, FAST_G * g.lv[l].wCell + 6);
         maxH = max(maxH, g.lv[l].hCell + 6);
-        P.listCap = max(P.listCap, g.lv[l].cellCap);
+        if (g.lv[l].wCell > 64) return cudaErrorNotSupported;       // a cell's columns must fit the 64-bit row masks of phase 4
     }
     const int need = ((maxW + 3 + 3) >> 2) + 2;        // + alignment slack + one spare word on each side
     const int PW = need <= 81 ? 81 : 135;              // odd pitches: rows start in different banks
     if (need > 135) return cudaErrorNotSupported;
     P.pitchW = PW;
     P.tileRows = maxH;
-    size_t smem = (size_t)4 * (PW * (3 * P.tileRows + 6) + FAST_G * P.listCap) + 4 * PW + 16;
+    P.bmWords = (PW + 7) / 8 + 2;
+    size_t smem = (size_t)4 * (PW * (3 * P.tileRows + 6) + P.tileRows * P.bmWords) + 16;
     if (smem > 200 * 1024) return cudaErrorNotSupported;
     dim3 grid(g.groupsPerFrame, nframes);
     return PW == 81 ? launch_fast_pw<81>(P, smem, grid, s) : launch_fast_pw<135>(P, smem, grid, s);
