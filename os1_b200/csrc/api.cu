@@ -25,7 +25,7 @@ struct DevBuf {
         if (p) cudaFree(p);
         p = nullptr; bytes = 0;
         cudaError_t e = cudaMalloc(&p, n);
-        if (e == cudaSuccess) bytes = n;
+        if (e == cudaSuccess) { bytes = n; e = cudaMemset(p, 0, n); }     // slots a frame does not fill read as zero, never as stale data
         return e;
     }
     void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
@@ -56,7 +56,7 @@ struct os1_orb {
     int batchCap = 0;
     PyramidPlan* plan = nullptr;        // small tiles (single frames)
     PyramidPlan* planBig = nullptr;     // larger tiles (batches)
-    DevBuf rtab, ptab, slab, cellCnt, stage, cand, code, node, candCount, lvKp, lvCount, status, outKp, outDesc, outCount;
+    DevBuf rtab, ptab, gtab, slab, cellCnt, stage, cand, code, node, candCount, lvKp, lvCount, status, outKp, outDesc, outCount;
     int lastFrames = 0;
     const uint8_t* lastLvl0 = nullptr; long long lastLvl0Stride = 0; int lastLvl0Pitch = 0;
     // pinned host mirrors for the host-buffer path
@@ -255,6 +255,16 @@ int build_geometry(os1_orb* h, int rows, int cols)
     CK(h->ptab.ensure(ptab.size() * sizeof(uint32_t)), "cudaMalloc(ptab)");
     CK(cudaMemcpy(h->rtab.p, rtab.data(), rtab.size() * sizeof(short4), cudaMemcpyHostToDevice), "upload resize tables");
     CK(cudaMemcpy(h->ptab.p, ptab.data(), ptab.size() * sizeof(uint32_t), cudaMemcpyHostToDevice), "upload path tables");
+    {
+        // one entry per FAST CTA of a frame, so the kernel neither searches its level nor divides by the groups per row
+        std::vector<int2> gtab;
+        for (int l = 0; l < L; l++)
+            for (int ci = 0; ci < g.lv[l].nRows; ci++)
+                for (int gj = 0; gj < g.lv[l].groupsPerRow; gj++) gtab.push_back(make_int2(l | (ci << 8), gj * FAST_G));
+        if (gtab.empty()) gtab.push_back(make_int2(0, 0));
+        CK(h->gtab.ensure(gtab.size() * sizeof(int2)), "cudaMalloc(gtab)");
+        CK(cudaMemcpy(h->gtab.p, gtab.data(), gtab.size() * sizeof(int2), cudaMemcpyHostToDevice), "upload FAST group table");
+    }
     if (h->plan) os1_pyramid_plan_destroy(h->plan);
     // coarsest-level tile: small for single frames (more CTAs), the plan is per resolution
     if (h->planBig) os1_pyramid_plan_destroy(h->planBig);
@@ -341,7 +351,7 @@ int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0
     const long long F = f0;
     d.lvl0 = lvl0 + F * lvl0Stride; d.lvl0FrameStride = lvl0Stride; d.lvl0Pitch = lvl0Pitch;
     d.slab = (uint8_t*)h->slab.p + F * g.slabBytes;
-    d.rtab = (const int16_t*)h->rtab.p; d.ptab = (const uint32_t*)h->ptab.p;
+    d.rtab = (const int16_t*)h->rtab.p; d.ptab = (const uint32_t*)h->ptab.p; d.gtab = (const int2*)h->gtab.p;
     d.cellCnt = (uint32_t*)h->cellCnt.p + F * g.cellsPerFrame;
     d.stage = (uint32_t*)h->stage.p + F * g.candPerFrame; d.cand = (uint32_t*)h->cand.p + F * g.candPerFrame;
     d.code = (uint32_t*)h->code.p + F * g.candPerFrame; d.node = (uint16_t*)h->node.p + F * g.candPerFrame;

@@ -32,6 +32,14 @@
 
 namespace {
 
+// n / d == (n * c_rcp.v[d]) >> 24 for d <= 256 while n * d < 2^24 (and n * v[d] < 2^32): every division of the kernel
+// is by a small CTA-uniform number, and an integer division costs ~25 instructions per thread
+struct RcpTab {
+    unsigned v[257];
+    constexpr RcpTab() : v() { for (int i = 1; i < 257; i++) v[i] = (1u << 24) / (unsigned)i + 1u; }
+};
+__constant__ RcpTab c_rcp = RcpTab();
+
 struct FastParams {
     Geometry g;
     DevPtrs d;
@@ -110,12 +118,9 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     extern __shared__ __align__(16) unsigned smw[];
     const Geometry& g = P.g;
     const int frame = blockIdx.y;
-    int level = 0;
-    while (level + 1 < g.nlevels && (int)blockIdx.x >= g.lv[level + 1].groupOff) level++;
+    const int2 gt = __ldg(P.d.gtab + blockIdx.x);
+    const int level = gt.x & 0xFF, ci = gt.x >> 8, j0 = gt.y;
     const LevelGeom& L = g.lv[level];
-    const int local = blockIdx.x - L.groupOff;
-    const int ci = local / L.groupsPerRow;
-    const int j0 = (local % L.groupsPerRow) * FAST_G;
     const int ncell = min(FAST_G, L.nCols - j0);
 
     const int x0 = OS1_BORDER + j0 * L.wCell;
@@ -156,8 +161,15 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     const int tr0 = 3, tr1 = th - 3;                          // tested rows
     const int wCell = L.wCell;
 
+    // tile: asynchronous 4-byte copies straight into shared memory (LDGSTS), all in flight at once — issued first, so
+    // the masks and the clearing below run while the bytes travel
+    for (int r = warp; r < th; r += FAST_THREADS / 32) {
+        const uint32_t* srow = (const uint32_t*)(src + (long long)(y0 + r) * spitch + xorg);
+        for (int w = lane; w < words; w += 32)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(img + r * pw + w)), "l"(srow + w) : "memory");
+    }
     // ---- phase 0/1: lane masks, tile -> shared, cleared score-map frame and bitmap ------------------------------------
-    const unsigned rcpW = 65536u / (unsigned)wCell + 1u;     // rel / wCell == (rel * rcpW) >> 16 while rel * wCell < 2^16
+    const unsigned rcpW = c_rcp.v[wCell];
     for (int w = tid; w < pw; w += FAST_THREADS) {
         unsigned vm[4], lm[4], rm[4];
 #pragma unroll
@@ -165,7 +177,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
             const int col = 4 * w + b;
             const bool in = col >= tc0 && col < tc1;
             const int rel = in ? col - tc0 : 1;
-            const int q = rel - (int)(((unsigned)rel * rcpW) >> 16) * wCell;       // rel % wCell
+            const int q = rel - (int)(((unsigned)rel * rcpW) >> 24) * wCell;       // rel % wCell
             vm[b] = in ? 0xFFFFu : 0u;
             lm[b] = (in && q == 0) ? 0u : 0xFFFFu;
             rm[b] = (in && (q == wCell - 1 || col == tc1 - 1)) ? 0u : 0xFFFFu;
@@ -176,12 +188,6 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     }
     for (int i = tid; i < th * bw; i += FAST_THREADS) bm[i] = 0;
     const int g0 = tc0 >> 2, g1 = (tc1 + 3) >> 2;
-    // tile: asynchronous 4-byte copies straight into shared memory (LDGSTS), all in flight at once
-    for (int r = warp; r < th; r += FAST_THREADS / 32) {
-        const uint32_t* srow = (const uint32_t*)(src + (long long)(y0 + r) * spitch + xorg);
-        for (int w = lane; w < words; w += 32)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(img + r * pw + w)), "l"(srow + w) : "memory");
-    }
     // the NMS reads one word / one row beyond the scored area: only that frame has to be zero
     for (int w = g0 - 1 + tid; w <= g1; w += FAST_THREADS) {
         scE[(tr0 - 1) * pw + w] = 0; scO[(tr0 - 1) * pw + w] = 0;
@@ -195,7 +201,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     __syncthreads();
 
     const int ng = g1 - g0, nItems = ng * (tr1 - tr0);
-    const unsigned rcpNg = (1u << 24) / (unsigned)ng + 1u;          // exact quotient for idx < 2^16 (nItems <= 136 * 64)
+    const unsigned rcpNg = c_rcp.v[ng];                             // exact quotient for idx < 2^16 (nItems <= 136 * 64)
     // stored s8 = strength - tmin; response = strength - 1 = s8 + tmin - 1
     const int iniS8 = g.iniTh - tmin + 1, minS8 = g.minTh - tmin + 1;
     // ---- phase 2: scores, four pixels per thread, kept packed ---------------------------------------------------------
@@ -231,8 +237,8 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     // another cell masked out; a pixel survives when it beats H3 of the rows above and below and H2 of its own row. -----
     {
         const int nr = tr1 - tr0;
-        const int nb = max(1, min(FAST_THREADS / ng, nr));                  // bands of rows
-        const int rpb = (nr + nb - 1) / nb;
+        const int nb = max(1, min(ng > 1 ? (int)(((unsigned)FAST_THREADS * rcpNg) >> 24) : FAST_THREADS, nr));     // bands of rows
+        const int rpb = (int)(((unsigned)(nr + nb - 1) * c_rcp.v[nb]) >> 24);
         const int band = (int)(((unsigned)tid * rcpNg) >> 24);
         const int gq = g0 + tid - band * ng;
         const int rb = tr0 + band * rpb, re = min(tr1, rb + rpb);

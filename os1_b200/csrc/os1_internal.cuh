@@ -66,6 +66,7 @@ struct DevPtrs {
     uint8_t* slab;              // pyramid slabs (levels >= 1; level 0 too when staged)
     const int16_t* rtab;        // resize tables, 4 x int16 per entry {ofs, c0, c1, pad}
     const uint32_t* ptab;       // quadtree path tables
+    const int2* gtab;           // FAST work groups of one frame: {level | cell row << 8, first cell column}
     uint32_t* cellCnt;          // [frame][cell]
     uint32_t* stage;            // [frame][candPerFrame]
     uint32_t* cand;             // [frame][candPerFrame]  ordered candidates
