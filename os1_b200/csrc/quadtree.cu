@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
 {
     extern __shared__ __align__(16) uint8_t smraw[];
     const Geometry& g = P.g;
-    const int level = blockIdx.x, frame = blockIdx.y;
+    const int level = blockIdx.y, frame = blockIdx.x;      // level-major launch order: the big levels first, the small ones fill the tail
     const LevelGeom& L = g.lv[level];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = L.quota;
@@ -392,7 +392,7 @@ cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes
     size_t smem = (size_t)P.sortCap * 8 + (size_t)(P.maxCells + 1) * 4 + (size_t)P.maxNodes * 4 * (4 + 4 + 2 + 2 + 1 + 1 + 1 + 1 + 1) + 8 * 4 +
                   (size_t)P.maxLeaves * 8 + 34 * 4;
     if (smem > 220 * 1024 || P.maxNodes > 16000) return cudaErrorNotSupported;
-    dim3 grid(g.nlevels, nframes);
+    dim3 grid(nframes, g.nlevels);
     // few frames: the level-0 CTA is the critical path, give it 1024 threads; batches: 512 threads, two CTAs per SM
     if (nframes <= 4) {
         if (smem > 48 * 1024) {
