@@ -31,12 +31,12 @@ struct PyrParams {
     const int4* xg;              // [level][ntx]  thread-mapping constants {ngroups, rcp, nbands, rcp}
     const int4* qtab;            // per level, per group of four destination columns: 2 x int4 (see QuadTaps)
     int qOff[OS1_MAX_LEVELS];    // first entry (in int4 units) of a level in qtab
-    const short4* rtab;          // resize tables {s0, s1, c0, c1}
+    const int4* ytab;            // per level, per destination row: {source row 0, source row 1, c0 << 12, c1 << 12}
+    int yOff[OS1_MAX_LEVELS];
     uint8_t* slab;
     long long slabBytes;
     int smemOff[OS1_MAX_LEVELS];
     int smemPitch[OS1_MAX_LEVELS];
-    int rxOff[OS1_MAX_LEVELS], ryOff[OS1_MAX_LEVELS];
     long long lvOff[OS1_MAX_LEVELS];
     int lvPitch[OS1_MAX_LEVELS];
 };
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
         const uint8_t* src = sm + p.smemOff[l - 1];
         uint32_t* dst = (uint32_t*)(sm + p.smemOff[l]);
         const int sp = p.smemPitch[l - 1], dpw = p.smemPitch[l] >> 2;
-        const short4* ry = p.rtab + p.ryOff[l];
+        const int4* ry = p.ytab + p.yOff[l];
         uint8_t* g = slab + p.lvOff[l];
         const int gp = p.lvPitch[l];
         if (ngroups > 0 && rows > 0) {
@@ -152,24 +152,29 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
                 const unsigned A0 = t1.x, A1 = t1.y, A2 = t1.z, A3 = t1.w;       // c0 | c1 << 16 per column
                 const int gxb = gx0 + 4 * grp;
                 const bool fullX = gxb >= X.z && gxb + 4 <= X.w;
-                const uint32_t* src32 = (const uint32_t*)src;
                 const int spw = sp >> 2;
+                const uint32_t* srcw = (const uint32_t*)src + wb - srcY0 * spw;      // word `wb` of global source row 0
                 auto hrow = [&](int srow, unsigned (&h)[4]) {
-                    const uint32_t* r = src32 + (srow - srcY0) * spw + wb;
+                    const uint32_t* r = srcw + srow * spw;
                     const unsigned w0 = r[0], w1 = r[1], w2 = r[2];
                     const unsigned B01 = __byte_perm(__byte_perm(w0, w1, selLo01), w2, selHi01);
                     const unsigned B23 = __byte_perm(__byte_perm(w0, w1, selLo23), w2, selHi23);
-                    // kept as ((H >> 4) << 16): the vertical pass then needs one multiply-high per tap
-                    h[0] = (__dp2a_lo(A0, B01, 0u) << 12) & 0xFFFF0000u;
-                    h[1] = (__dp2a_hi(A1, B01, 0u) << 12) & 0xFFFF0000u;
-                    h[2] = (__dp2a_lo(A2, B23, 0u) << 12) & 0xFFFF0000u;
-                    h[3] = (__dp2a_hi(A3, B23, 0u) << 12) & 0xFFFF0000u;
+                    // H with its low four bits cleared: (c << 12) * (H & ~15) >> 32 == (c * (H >> 4)) >> 16, so the
+                    // vertical pass is one multiply-high per tap
+                    h[0] = __dp2a_lo(A0, B01, 0u) & ~15u;
+                    h[1] = __dp2a_hi(A1, B01, 0u) & ~15u;
+                    h[2] = __dp2a_lo(A2, B23, 0u) & ~15u;
+                    h[3] = __dp2a_hi(A3, B23, 0u) & ~15u;
                 };
                 unsigned h0[4], h1[4] = { 0, 0, 0, 0 };
                 int prev1 = -1;
-                for (int ly = yb; ly < ye; ly++) {
-                    const int gy = Y.x + ly;
-                    const short4 ey = __ldg(ry + gy);
+                const int4* ryp = ry + Y.x + yb;
+                uint32_t* dp = dst + yb * dpw + grp;
+                uint8_t* grow = g + (long long)(Y.x + yb) * gp + gxb;
+                // rows of the band this tile owns (the others are halo for the next level): [o0, o1)
+                const int o0 = max(Y.z - Y.x, yb), o1 = min(Y.w - Y.x, ye);
+                for (int ly = yb; ly < ye; ly++, ryp++, dp += dpw, grow += gp) {
+                    const int4 ey = __ldg(ryp);
                     if (ey.x == prev1) {
 #pragma unroll
                         for (int i = 0; i < 4; i++) h0[i] = h1[i];
@@ -188,9 +193,8 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
                         const unsigned v = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
                         word |= v << (8 * i);
                     }
-                    dst[ly * dpw + grp] = word;
-                    if (gy >= Y.z && gy < Y.w) {
-                        uint8_t* grow = g + (long long)gy * gp + gxb;
+                    *dp = word;
+                    if (ly >= o0 && ly < o1) {
                         if (fullX) *(uint32_t*)grow = word;
                         else {
 #pragma unroll
@@ -214,6 +218,7 @@ struct PyramidPlan {
     int4* d_yt = nullptr;
     int4* d_xg = nullptr;
     int4* d_qtab = nullptr;
+    int4* d_ytab = nullptr;
     bool tapsFit = true;       // every group of four columns finds its eight taps in three consecutive source words
     PyrParams prm;
     int boxW, boxH;
@@ -322,6 +327,18 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
                 q.push_back(make_int4((int)A[0], (int)A[1], (int)A[2], (int)A[3]));
             }
         }
+        // vertical taps per destination row, coefficients pre-shifted for the multiply-high of the vertical pass
+        std::vector<int4> yt4;
+        for (int l = 1; l < g.nlevels; l++) {
+            p.yOff[l] = (int)yt4.size();
+            std::vector<short> s0, s1, c0, c1;
+            os1_host_resize_taps(g.lv[l - 1].h, g.lv[l].h, true, s0, s1, c0, c1);
+            for (int y = 0; y < g.lv[l].h; y++) yt4.push_back(make_int4(s0[y], s1[y], (int)c0[y] << 12, (int)c1[y] << 12));
+        }
+        if (yt4.empty()) yt4.push_back(make_int4(0, 0, 0, 0));
+        cudaMalloc(&P->d_ytab, yt4.size() * sizeof(int4));
+        cudaMemcpy(P->d_ytab, yt4.data(), yt4.size() * sizeof(int4), cudaMemcpyHostToDevice);
+        p.ytab = P->d_ytab;
         if (q.empty()) q.push_back(make_int4(0, 0, 0, 0));
         cudaMalloc(&P->d_qtab, q.size() * sizeof(int4));
         cudaMemcpy(P->d_qtab, q.data(), q.size() * sizeof(int4), cudaMemcpyHostToDevice);
@@ -336,7 +353,6 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         p.smemPitch[l] = (l == 0) ? P->boxW : ((mw[l] + 3 + 3) & ~3);     // + up to 3 bytes: column 0 sits on a 4-px boundary
         off += (size_t)p.smemPitch[l] * mh[l];
         off = (off + 127) & ~(size_t)127;
-        p.rxOff[l] = g.lv[l].rxOff; p.ryOff[l] = g.lv[l].ryOff;
         p.lvOff[l] = g.lv[l].off; p.lvPitch[l] = g.lv[l].pitch;
     }
     p.slabBytes = g.slabBytes;
@@ -365,7 +381,7 @@ bool os1_pyramid_plan_ok(const PyramidPlan* P)
 void os1_pyramid_plan_destroy(PyramidPlan* P)
 {
     if (!P) return;
-    cudaFree(P->d_xt); cudaFree(P->d_yt); cudaFree(P->d_xg); cudaFree(P->d_qtab);
+    cudaFree(P->d_xt); cudaFree(P->d_yt); cudaFree(P->d_xg); cudaFree(P->d_qtab); cudaFree(P->d_ytab);
     delete P;
 }
 
@@ -382,7 +398,6 @@ cudaError_t os1_launch_pyramid(PyramidPlan* P, const Geometry& g, const DevPtrs&
                            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
     PyrParams p = P->prm;
-    p.rtab = (const short4*)d.rtab;
     p.slab = d.slab;
     dim3 grid(P->ntx, P->nty, nframes), block(32, 8);
     p.dbgLvl0 = d.lvl0; p.dbgStride = d.lvl0FrameStride; p.dbgPitch = d.lvl0Pitch; p.dbgW = g.cols; p.dbgH = g.rows;
