@@ -44,8 +44,8 @@ struct os1_orb {
     int device;
     cudaStream_t ownStream = nullptr, stream = nullptr;
     cudaStream_t inStream = nullptr, outStream = nullptr;       // upload / download streams of the chunked host path
-    cudaStream_t altStream = nullptr;                           // second compute stream: odd chunks, so one chunk's tail waves overlap the next
-    cudaEvent_t altEv = nullptr;
+    cudaStream_t altStream[3] = { nullptr, nullptr, nullptr };  // extra compute streams: chunks rotate over them, so one chunk's
+    cudaEvent_t altEv[3] = { nullptr, nullptr, nullptr };       // partial last waves overlap the next chunk's kernels
     std::vector<cudaEvent_t> chunkEv;                           // 2 per chunk: uploaded, computed
     std::string err;
 
@@ -427,8 +427,10 @@ int os1_orb_destroy(os1_orb* h)
     if (h->hostStatus) cudaFreeHost(h->hostStatus);
     for (int i = 0; i < 5; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (cudaEvent_t e : h->chunkEv) cudaEventDestroy(e);
-    if (h->altStream) cudaStreamDestroy(h->altStream);
-    if (h->altEv) cudaEventDestroy(h->altEv);
+    for (int i = 0; i < 3; i++) {
+        if (h->altStream[i]) cudaStreamDestroy(h->altStream[i]);
+        if (h->altEv[i]) cudaEventDestroy(h->altEv[i]);
+    }
     if (h->inStream) cudaStreamDestroy(h->inStream);
     if (h->outStream) cudaStreamDestroy(h->outStream);
     if (h->ownStream) cudaStreamDestroy(h->ownStream);
@@ -600,7 +602,7 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
 
     // ---- batches with host buffers: chunks flow through upload -> kernels -> download on three streams, so the PCIe
     // copies of neighbouring chunks hide behind the kernels of the current one ----------------------------------------------
-    int chunk = 64;
+    int chunk = 16;
     if (const char* e = getenv("OS1_CHUNK")) chunk = std::max(1, atoi(e));
     // chunk boundaries: a geometric ramp.  The upload of chunk c+1 hides behind the kernels of chunk c only while it is
     // not longer than them, so chunks grow by less than the kernel-time / upload-time ratio per frame (1.31 at 720p over
@@ -628,18 +630,20 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     CK(cudaStreamWaitEvent(h->outStream, h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
     // odd chunks run on a second compute stream (their scratch is disjoint): the partial last waves of one chunk's
     // kernels are filled by the other chunk's
-    static const bool useAlt = !(getenv("OS1_ALT") && atoi(getenv("OS1_ALT")) == 0);
-    const bool alt = useAlt && nchunks > 1;
+    static const int nAlt = getenv("OS1_ALT") ? std::min(3, std::max(0, atoi(getenv("OS1_ALT")))) : 2;
+    const bool alt = nAlt > 0 && nchunks > 1;
     if (alt) {
-        if (!h->altStream) CK(cudaStreamCreateWithFlags(&h->altStream, cudaStreamNonBlocking), "cudaStreamCreate");
-        if (!h->altEv) CK(cudaEventCreateWithFlags(&h->altEv, cudaEventDisableTiming), "cudaEventCreate");
-        CK(cudaStreamWaitEvent(h->altStream, h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
+        for (int i = 0; i < nAlt; i++) {
+            if (!h->altStream[i]) CK(cudaStreamCreateWithFlags(&h->altStream[i], cudaStreamNonBlocking), "cudaStreamCreate");
+            if (!h->altEv[i]) CK(cudaEventCreateWithFlags(&h->altEv[i], cudaEventDisableTiming), "cudaEventCreate");
+            CK(cudaStreamWaitEvent(h->altStream[i], h->chunkEv[2 * nchunks], 0), "cudaStreamWaitEvent");
+        }
     }
     const size_t kpRow = (size_t)dCap * sizeof(os1_kp_dev), dRow = (size_t)dCap * 32;
     const int copyCap = std::min(dCap, cap_per_frame);
     for (int c = 0; c < nchunks; c++) {
         const int f0 = cuts[c], n = cuts[c + 1] - cuts[c];
-        cudaStream_t cs = (alt && (c & 1)) ? h->altStream : h->stream;
+        cudaStream_t cs = (alt && c % (nAlt + 1)) ? h->altStream[c % (nAlt + 1) - 1] : h->stream;
         if (!direct) {
             CK(stage_in(f0, n, frames_on_device ? cs : h->inStream), "upload frames");
             if (!frames_on_device) {
@@ -661,8 +665,10 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
         }
     }
     if (alt) {       // join: everything queued on the second stream is ordered before what follows on the handle's stream
-        CK(cudaEventRecord(h->altEv, h->altStream), "cudaEventRecord");
-        CK(cudaStreamWaitEvent(h->stream, h->altEv, 0), "cudaStreamWaitEvent");
+        for (int i = 0; i < nAlt; i++) {
+            CK(cudaEventRecord(h->altEv[i], h->altStream[i]), "cudaEventRecord");
+            CK(cudaStreamWaitEvent(h->stream, h->altEv[i], 0), "cudaStreamWaitEvent");
+        }
     }
     CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
     CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");

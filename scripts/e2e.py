@@ -17,7 +17,8 @@ kh = torch.empty((B, cap, 28), dtype=torch.uint8).pin_memory(); dh = torch.empty
 ch = torch.zeros(B, dtype=torch.int32).pin_memory()
 def sd(): ext.extract_batch_raw(fd.data_ptr(), B, ROWS, COLS, COLS, ROWS * COLS, True, kd.data_ptr(), dd.data_ptr(), cap, cd.data_ptr(), True)
 def se(): ext.extract_batch_raw(fh.data_ptr(), B, ROWS, COLS, COLS, ROWS * COLS, False, kh.data_ptr(), dh.data_ptr(), cap, ch.data_ptr(), False)
-for f, name in ((sd, "device"), (se, "e2e")):
+def sm(): ext.extract_batch_raw(fd.data_ptr(), B, ROWS, COLS, COLS, ROWS * COLS, True, kh.data_ptr(), dh.data_ptr(), cap, ch.data_ptr(), False)
+for f, name in ((sd, "device"), (se, "e2e"), (sm, "device frames -> host outputs (chunked)")):
     for _ in range(5): f()
     torch.cuda.synchronize(); t = time.perf_counter()
     for _ in range(steps): f()
