@@ -87,26 +87,34 @@ __device__ __forceinline__ void arc_extremes(const unsigned (&W)[7][3], unsigned
     r[13] = ring_pair<-3, ODD>(W[4][0], W[4][1], W[4][2]);
     r[14] = ring_pair<-2, ODD>(W[5][0], W[5][1], W[5][2]);
     r[15] = ring_pair<-1, ODD>(W[6][0], W[6][1], W[6][2]);
-    unsigned lo3[16], hi3[16];
+    // Arcs 2i and 2i+1 share the eight ring values 2i+1 .. 2i+8 (four adjacent pairs), and
+    //   max(min(W, r[2i]), min(W, r[2i+9])) == min(W, max(r[2i], r[2i+9])),
+    // so each polarity takes 8 pair ops + 8 pair-of-pairs + 8 end ops + 8 min3/max3 + 4 to fold: 36 instead of the 40 of
+    // a sliding window-3 / window-9 scheme.
+    unsigned pl[8], ph[8];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        lo3[k] = __vimin3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
-        hi3[k] = __vimax3_u16x2(r[k], r[(k + 1) & 15], r[(k + 2) & 15]);
+    for (int j = 0; j < 8; j++) {
+        pl[j] = __vminu2(r[2 * j + 1], r[(2 * j + 2) & 15]);
+        ph[j] = __vmaxu2(r[2 * j + 1], r[(2 * j + 2) & 15]);
     }
-    unsigned lo9[16], hi9[16];
+    unsigned ql[8], qh[8];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        lo9[k] = __vimin3_u16x2(lo3[k], lo3[(k + 3) & 15], lo3[(k + 6) & 15]);      // min of ring[k..k+8]
-        hi9[k] = __vimax3_u16x2(hi3[k], hi3[(k + 3) & 15], hi3[(k + 6) & 15]);
+    for (int j = 0; j < 8; j++) {
+        ql[j] = __vminu2(pl[j], pl[(j + 1) & 7]);
+        qh[j] = __vmaxu2(ph[j], ph[(j + 1) & 7]);
     }
-    unsigned d = __vimax3_u16x2(lo9[0], lo9[1], lo9[2]), b = __vimin3_u16x2(hi9[0], hi9[1], hi9[2]);
+    unsigned vd[8], vb[8];
 #pragma unroll
-    for (int k = 3; k < 15; k += 2) {
-        d = __vimax3_u16x2(d, lo9[k], lo9[k + 1]);
-        b = __vimin3_u16x2(b, hi9[k], hi9[k + 1]);
+    for (int i = 0; i < 8; i++) {
+        const unsigned ehi = __vmaxu2(r[2 * i], r[(2 * i + 9) & 15]), elo = __vminu2(r[2 * i], r[(2 * i + 9) & 15]);
+        vd[i] = __vimin3_u16x2(ql[i], ql[(i + 2) & 7], ehi);       // the better of arcs 2i, 2i+1: min over the arc
+        vb[i] = __vimax3_u16x2(qh[i], qh[(i + 2) & 7], elo);       // ... max over the arc
     }
-    darkest = __vimax3_u16x2(d, lo9[15], lo9[15]);
-    brightest = __vimin3_u16x2(b, hi9[15], hi9[15]);
+    unsigned d = __vimax3_u16x2(vd[0], vd[1], vd[2]), bb = __vimin3_u16x2(vb[0], vb[1], vb[2]);
+    d = __vimax3_u16x2(d, vd[3], vd[4]); bb = __vimin3_u16x2(bb, vb[3], vb[4]);
+    d = __vimax3_u16x2(d, vd[5], vd[6]); bb = __vimin3_u16x2(bb, vb[5], vb[6]);
+    darkest = __vmaxu2(d, vd[7]);
+    brightest = __vminu2(bb, vb[7]);
 }
 
 // u16x2 lanes holding value*257: per-lane saturating difference without any cross-lane borrow
