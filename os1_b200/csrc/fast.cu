@@ -14,9 +14,9 @@
 // A CTA handles FAST_G horizontally adjacent cells of one cell row.  The work is integer-issue bound, so the
 // kernel is organised around instruction count, not bytes:
 //   phase 1  tile -> shared memory as aligned 32-bit words;
-//   phase 2  a thread scores FOUR adjacent pixels from 21 word loads: each ring value of a pixel pair is lifted
-//            into a u16x2 register by ONE byte-permute (value*257 per half-word, order preserving) and the
-//            min-of-9 / max-of-9 arcs are min3(min3) chains on the packed VIMNMX3.U16x2 path (2 pixels/instr);
+//   phase 2  a thread scores FOUR adjacent pixels from 21 word loads: each ring value of a pixel pair sits in the high
+//            bytes of a u16x2 register (at most one byte-permute or shift, see ring_pair) and the min-of-9 / max-of-9
+//            arcs are min/max trees on the packed VIMNMX.U16x2 path (2 pixels/instr, 36 per polarity);
 //            the response is finished in packed form too (saturating differences as max(a,b)-b, no cross-lane
 //            borrow) and stored as max(strength - tmin, 0): zero below min(iniTh, minTh), which leaves NMS
 //            unchanged and makes the maps sparse;
@@ -50,19 +50,23 @@ struct FastParams {
 
 // ---- packed ring access -------------------------------------------------------------------------------------
 // The three words (wm, w0, wp) of a tile row hold bytes -4..7 relative to the first of the thread's four pixels.
-// ring_pair<DX, ODD> returns, for the pixel pair (ODD ? {1,3} : {0,2}), the bytes at horizontal offset DX as
-// u16x2 with each half-word = byte * 257.
+// ring_pair<DX, ODD> returns, for the pixel pair (ODD ? {1,3} : {0,2}), the bytes at horizontal offset DX in the HIGH
+// bytes of the two u16 lanes; the low bytes hold whatever neighbours them in memory.  min/max of such lanes order by
+// the high byte first, so a chain of them ends with the exact min/max of the pixel values in the high bytes — and the
+// value needed is simply the 32-bit window at byte offset o = 3 + DX + ODD of the row: a register as it is (o = 0, 4),
+// one shift (o = 3, 7; IMAD.SHL, not on the saturated ALU pipe) or one byte-permute (the rest), 18 permutes per four
+// pixels instead of 32.
 template <int DX, int ODD>
 __device__ __forceinline__ unsigned ring_pair(unsigned wm, unsigned w0, unsigned wp)
 {
-    constexpr int pa = DX + ODD, pb = pa + 2;
-    if (DX <= 0) {
-        constexpr unsigned ia = pa + 4, ib = pb + 4;
-        return __byte_perm(wm, w0, ia | (ia << 4) | (ib << 8) | (ib << 12));
-    } else {
-        constexpr unsigned ia = pa, ib = pb;
-        return __byte_perm(w0, wp, ia | (ia << 4) | (ib << 8) | (ib << 12));
-    }
+    constexpr int o = 3 + DX + ODD;
+    static_assert(o >= 0 && o <= 7, "ring offset outside the three words");
+    if (o == 0) return wm;
+    if (o == 4) return w0;
+    if (o == 3) return w0 << 8;
+    if (o == 7) return wp << 8;
+    if (o < 3) return __byte_perm(wm, w0, ((o + 1) << 4) | ((o + 3) << 12));             // bytes o+1, o+3 of (wm, w0)
+    return __byte_perm(w0, wp, ((o - 3) << 4) | ((o - 1) << 12));                          // bytes o-3, o-1 of (w0, wp)
 }
 
 // max over the 16 arcs of 9 of (min ring), min over the arcs of (max ring), for one pixel pair
@@ -117,7 +121,7 @@ __device__ __forceinline__ void arc_extremes(const unsigned (&W)[7][3], unsigned
     brightest = __vminu2(bb, vb[7]);
 }
 
-// u16x2 lanes holding value*257: per-lane saturating difference without any cross-lane borrow
+// per-lane saturating difference of u16x2 lanes without any cross-lane borrow
 __device__ __forceinline__ unsigned usubsat2(unsigned a, unsigned b) { return __vmaxu2(a, b) - b; }     // max(a-b, 0)
 
 template <int PW>
@@ -186,7 +190,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
             const bool in = col >= tc0 && col < tc1;
             const int rel = in ? col - tc0 : 1;
             const int q = rel - (int)(((unsigned)rel * rcpW) >> 24) * wCell;       // rel % wCell
-            vm[b] = in ? 0xFFFFu : 0u;
+            vm[b] = in ? 0xFF00u : 0u;
             lm[b] = (in && q == 0) ? 0u : 0xFFFFu;
             rm[b] = (in && (q == wCell - 1 || col == tc1 - 1)) ? 0u : 0xFFFFu;
         }
@@ -214,7 +218,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     const int iniS8 = g.iniTh - tmin + 1, minS8 = g.minTh - tmin + 1;
     // ---- phase 2: scores, four pixels per thread, kept packed ---------------------------------------------------------
     {
-        const unsigned T = (unsigned)tmin * 0x01010101u;       // tmin * 257 in both lanes
+        const unsigned T = (unsigned)tmin * 0x01000100u;       // tmin << 8 in both lanes
         // (rows x groups flattened so that every lane has work: 75 groups per row would leave a third of the lanes
         //  idle in the last of three 32-wide trips; the division by the group count is a multiply by its reciprocal)
         for (int idx = tid; idx < nItems; idx += FAST_THREADS) {
@@ -229,12 +233,15 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
                 unsigned dE, bE, dO, bO;
                 arc_extremes<0>(W, dE, bE);
                 arc_extremes<1>(W, dO, bO);
-                const unsigned cE = __byte_perm(W[3][1], 0, 0x2200), cO = __byte_perm(W[3][1], 0, 0x3311);
-                // strength*257 = max(darkest - c, c - brightest) per lane; stored value = max(strength - tmin, 0)*257,
+                // centre pixels in the high bytes; low bytes 0x00 for `ring - centre`, 0xFF for `centre - ring`, so the
+                // unknown low bytes of the ring extremes can neither borrow from nor carry into the high byte
+                const unsigned cE = __byte_perm(W[3][1], 0, 0x2404), cO = __byte_perm(W[3][1], 0, 0x3414);
+                const unsigned cEf = cE | 0x00FF00FFu, cOf = cO | 0x00FF00FFu;
+                // high byte of a lane = max(darkest - c, c - brightest) = strength; stored = max(strength - tmin, 0) << 8,
                 // i.e. non-zero exactly when the cv::FAST response (strength-1) reaches tmin — order preserving for NMS
-                const unsigned sE = __vmaxu2(usubsat2(dE, cE), usubsat2(cE, bE));
-                const unsigned sO = __vmaxu2(usubsat2(dO, cO), usubsat2(cO, bO));
-                scE[r * pw + gq] = usubsat2(sE, T) & vmE[gq];
+                const unsigned sE = __vmaxu2(usubsat2(dE, cE), usubsat2(cEf, bE));
+                const unsigned sO = __vmaxu2(usubsat2(dO, cO), usubsat2(cOf, bO));
+                scE[r * pw + gq] = usubsat2(sE, T) & vmE[gq];        // (the masks also clear the low bytes)
                 scO[r * pw + gq] = usubsat2(sO, T) & vmO[gq];
             }
     }
@@ -278,7 +285,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
                 unsigned en, on, h2En, h3En, h2On, h3On;
                 hrow(r + 1, en, on, h2En, h3En, h2On, h3On);
                 const unsigned mE = __vimax3_u16x2(h3Ep, h2Ec, h3En), mO = __vimax3_u16x2(h3Op, h2Oc, h3On);
-                // lanes that beat all eight neighbours -> 1 (a non-zero difference of two multiples of 257 is >= 257)
+                // lanes that beat all eight neighbours -> 1
                 const unsigned nE = __vminu2(__vmaxu2(ec, mE) - mE, ONES), nO = __vminu2(__vmaxu2(oc, mO) - mO, ONES);
                 const unsigned x = 2u * nO + nE;                                  // bits 0,1 <-> pixels 0,1; bits 16,17 <-> pixels 2,3
                 const unsigned nib = (x | (x >> 14)) & 0xFu;
