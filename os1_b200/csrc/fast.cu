@@ -46,6 +46,7 @@ struct FastParams {
     int pitchW;         // shared-memory row pitch in 32-bit words
     int tileRows;
     int bmWords;        // words per row of the survivor bitmap (one bit per tile byte column, + 2 spare)
+    int listStride;     // u16 slots per warp for the survivor list of a cell (aliases the image tile)
 };
 
 // ---- packed ring access -------------------------------------------------------------------------------------
@@ -297,67 +298,61 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     }
     __syncthreads();
 
-    // ---- phase 4: per cell, one lane per row — the survivors >= iniTh if there are any, else those >= minTh (the reference's
-    // retry with minThFAST, ORBextractor.cc:852-856), emitted in row-major order (cv::FAST's) ---------------------------
+    // ---- phase 4: per cell (one warp).  Pass A, lanes = rows: cut the cell's columns out of the row bitmaps and write
+    // the survivors, in row-major order (cv::FAST's), to a list in the dead image tile.  Pass B, lanes = survivors: vote
+    // "any survivor >= iniTh", keep those or else the ones >= minTh (the reference's retry with minThFAST,
+    // ORBextractor.cc:852-856) and emit them at their rank among the kept ones. -------------------------------------
     for (int cc = warp; cc < ncell; cc += FAST_THREADS / 32) {
         const int cx0 = tc0 + cc * wCell, cx1 = min(cx0 + wCell, tc1);      // tile byte columns of the cell (at most 64)
         const int wsel = cx0 >> 5, bsh = cx0 & 31, width = cx1 - cx0;
         const unsigned keepLo = width >= 32 ? 0xFFFFFFFFu : ((1u << width) - 1u);
         const unsigned keepHi = width >= 64 ? 0xFFFFFFFFu : (width > 32 ? ((1u << (width - 32)) - 1u) : 0u);
         uint32_t* out = P.d.stage + (long long)frame * g.candPerFrame + L.candOff + (long long)(ci * L.nCols + j0 + cc) * L.cellCap;
-        // score byte (strength - tmin) of tile byte column c in row r
-        auto score8 = [&](int r, int c) -> int {
-            const unsigned v = ((c & 1) ? scO : scE)[r * pw + (c >> 2)];
-            return (int)(((c & 2) ? (v >> 24) : (v >> 8)) & 0xFFu);
-        };
-        // the cell's survivors in row r, and which of them reach iniTh / minTh
-        auto classify = [&](int r, unsigned& sLo, unsigned& sHi, unsigned& pLo, unsigned& pHi) {
-            sLo = sHi = pLo = pHi = 0;
-            if (r >= tr1) return;
-            const unsigned* w = bm + r * bw + wsel;
-            const unsigned w0 = w[0], w1 = w[1], w2 = w[2];
-            unsigned a = __funnelshift_r(w0, w1, bsh) & keepLo, b = __funnelshift_r(w1, w2, bsh) & keepHi;
-            while (a | b) {
-                const bool inLo = a != 0;
-                const int bit = inLo ? __ffs(a) - 1 : __ffs(b) - 1;
-                if (inLo) a &= a - 1; else b &= b - 1;
-                const int s8 = score8(r, cx0 + bit + (inLo ? 0 : 32));
-                const unsigned m = 1u << bit;
-                if (s8 >= iniS8) { if (inLo) sLo |= m; else sHi |= m; }
-                if (s8 >= minS8) { if (inLo) pLo |= m; else pHi |= m; }
-            }
-        };
-        const bool oneTrip = tr1 - tr0 <= 32;             // (cells with more than 32 tested rows take several trips)
-        unsigned sLo, sHi, pLo, pHi;
-        bool st = false;
-        for (int r0 = tr0; r0 < tr1; r0 += 32) {
-            classify(r0 + lane, sLo, sHi, pLo, pHi);
-            st = st || (sLo | sHi) != 0;
-        }
-        const bool strong = __any_sync(0xffffffffu, st);
-        int base = 0;
-        for (int r0 = tr0; r0 < tr1; r0 += 32) {
+        unsigned short* list = (unsigned short*)img + warp * P.listStride;      // entries: row << 6 | column inside the cell
+        int n = 0;
+        for (int r0 = tr0; r0 < tr1; r0 += 32) {                                // (cells taller than 32 tested rows: two trips)
             const int r = r0 + lane;
-            if (!oneTrip) classify(r, sLo, sHi, pLo, pHi);       // one trip: the vote's masks are this trip's
-            unsigned mLo = strong ? sLo : pLo, mHi = strong ? sHi : pHi;
-            const int cnt = __popc(mLo) + __popc(mHi);
+            unsigned lo = 0, hi = 0;
+            if (r < tr1) {
+                const unsigned* w = bm + r * bw + wsel;
+                const unsigned w0 = w[0], w1 = w[1], w2 = w[2];
+                lo = __funnelshift_r(w0, w1, bsh) & keepLo;
+                hi = __funnelshift_r(w1, w2, bsh) & keepHi;
+            }
+            const int cnt = __popc(lo) + __popc(hi);
             int incl = cnt;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 const int t = __shfl_up_sync(0xffffffffu, incl, d);
                 if (lane >= d) incl += t;
             }
-            int rank = base + incl - cnt;
-            base += __shfl_sync(0xffffffffu, incl, 31);
-            while (mLo | mHi) {
-                const bool inLo = mLo != 0;
-                const int bit = inLo ? __ffs(mLo) - 1 : __ffs(mHi) - 1;
-                if (inLo) mLo &= mLo - 1; else mHi &= mHi - 1;
-                const int col = cx0 + bit + (inLo ? 0 : 32);
-                const int s8 = score8(r, col);
-                if (rank < L.cellCap) out[rank] = OS1_PACK_XYS(col + xorg - OS1_BORDER, r + y0 - OS1_BORDER, s8 + tmin - 1);
-                rank++;
-            }
+            unsigned short* dst = list + n + incl - cnt;
+            const unsigned tag = (unsigned)r << 6;
+            while (lo) { *dst++ = (unsigned short)(tag | (unsigned)(__ffs(lo) - 1)); lo &= lo - 1; }
+            while (hi) { *dst++ = (unsigned short)(tag | (unsigned)(__ffs(hi) + 31)); hi &= hi - 1; }
+            n += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        __syncwarp();
+        // score byte (strength - tmin) of list entry e
+        auto score8 = [&](unsigned e) -> int {
+            const int r = e >> 6, c = cx0 + (int)(e & 63u);
+            const unsigned v = ((c & 1) ? scO : scE)[r * pw + (c >> 2)];
+            return (int)(((c & 2) ? (v >> 24) : (v >> 8)) & 0xFFu);
+        };
+        unsigned e = 0; int s8 = 0;
+        bool st = false;
+        for (int i = lane; i < n; i += 32) { e = list[i]; s8 = score8(e); st = st || s8 >= iniS8; }
+        const int lim = __any_sync(0xffffffffu, st) ? iniS8 : minS8;
+        int base = 0;
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            const int i = i0 + lane;
+            if (n > 32 && i < n) { e = list[i]; s8 = score8(e); }       // up to 32 survivors: the vote's registers are this trip's
+            const bool pass = i < n && s8 >= lim;
+            const unsigned bal = __ballot_sync(0xffffffffu, pass);
+            const int rank = base + __popc(bal & ((1u << lane) - 1u));
+            if (pass && rank < L.cellCap)
+                out[rank] = OS1_PACK_XYS(cx0 + (int)(e & 63u) + xorg - OS1_BORDER, (int)(e >> 6) + y0 - OS1_BORDER, s8 + tmin - 1);
+            base += __popc(bal);
         }
         if (lane == 0) cellCnt[cc] = min(base, L.cellCap);
     }
@@ -382,11 +377,12 @@ cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cu
     if (g.groupsPerFrame == 0) return cudaSuccess;
     FastParams P;
     P.g = g; P.d = d;
-    int maxW = 0, maxH = 0;
+    int maxW = 0, maxH = 0, maxCap = 1;
     for (int l = 0; l < g.nlevels; l++) {
         if (g.lv[l].nCells == 0) continue;
         maxW = max(maxW, FAST_G * g.lv[l].wCell + 6);
         maxH = max(maxH, g.lv[l].hCell + 6);
+        maxCap = max(maxCap, g.lv[l].cellCap);
         if (g.lv[l].wCell > 64) return cudaErrorNotSupported;       // a cell's columns must fit the 64-bit row masks of phase 4
     }
     const int need = ((maxW + 3 + 3) >> 2) + 2;        // + alignment slack + one spare word on each side
@@ -395,6 +391,8 @@ cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cu
     P.pitchW = PW;
     P.tileRows = maxH;
     P.bmWords = (PW + 7) / 8 + 2;
+    P.listStride = (maxCap + 1) & ~1;
+    if ((size_t)2 * P.listStride * (FAST_THREADS / 32) > (size_t)4 * PW * P.tileRows) return cudaErrorNotSupported;
     size_t smem = (size_t)4 * (PW * (3 * P.tileRows + 6) + P.tileRows * P.bmWords) + 16;
     if (smem > 200 * 1024) return cudaErrorNotSupported;
     dim3 grid(g.groupsPerFrame, nframes);
