@@ -153,9 +153,9 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     unsigned* lmO = lmE + pw;
     unsigned* rmE = lmO + pw;                    // 0 in the lane whose pixel is a cell's LAST tested column
     unsigned* rmO = rmE + pw;
-    unsigned* bm = rmO + pw;                     // [tileRows][bmWords]: bit c of a row <-> tile byte column c survived the NMS
+    unsigned* bm = smw + ((pw * (3 * P.tileRows + 6) + 3) & ~3);      // [tileRows][bmWords] (16-byte aligned): bit c of a row <-> tile byte column c survived the NMS
     const int bw = P.bmWords;
-    const int xorg = (x0 & ~3) - 4;             // global x of tile byte 0 (one spare word on the left)
+    const int xorg = (x0 - 1) & ~15;            // global x of tile byte 0: 16-byte aligned, at least one spare word on the left
     const int words = ((x1 + 3 - xorg) >> 2) + 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -174,12 +174,26 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     const int tr0 = 3, tr1 = th - 3;                          // tested rows
     const int wCell = L.wCell;
 
-    // tile: asynchronous 4-byte copies straight into shared memory (LDGSTS), all in flight at once — issued first, so
-    // the masks and the clearing below run while the bytes travel
-    for (int r = warp; r < th; r += FAST_THREADS / 32) {
-        const uint32_t* srow = (const uint32_t*)(src + (long long)(y0 + r) * spitch + xorg);
-        for (int w = lane; w < words; w += 32)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(img + r * pw + w)), "l"(srow + w) : "memory");
+    // tile: asynchronous 16-byte copies straight into shared memory (LDGSTS), all in flight at once — issued first, so
+    // the masks and the clearing below run while the bytes travel.  (Level rows start 16-byte aligned and have a pitch
+    // that is a multiple of 16; a chunk that would end beyond the level's last column is fetched word by word, so that
+    // nothing is ever read past the end of a frame the caller owns.)
+    {
+        const int nch = (words + 3) >> 2;                   // 16-byte chunks per tile row
+        const unsigned rcpCh = c_rcp.v[nch];
+        const int lw = L.w;
+        for (int i = tid; i < th * nch; i += FAST_THREADS) {
+            const int r = (int)(((unsigned)i * rcpCh) >> 24), c = i - r * nch;
+            const uint8_t* gsrc = src + (long long)(y0 + r) * spitch + xorg + 16 * c;
+            const unsigned sdst = (unsigned)__cvta_generic_to_shared(img + r * pw + 4 * c);
+            if (xorg + 16 * c + 16 <= lw) {
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(gsrc) : "memory");
+            } else {
+                for (int k = 0; k < 4; k++)
+                    if (4 * c + k < words)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sdst + 4 * k), "l"(gsrc + 4 * k) : "memory");
+            }
+        }
     }
     // ---- phase 0/1: lane masks, tile -> shared, cleared score-map frame and bitmap ------------------------------------
     const unsigned rcpW = c_rcp.v[wCell];
@@ -199,7 +213,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
         lmE[w] = lm[0] | (lm[2] << 16); lmO[w] = lm[1] | (lm[3] << 16);
         rmE[w] = rm[0] | (rm[2] << 16); rmO[w] = rm[1] | (rm[3] << 16);
     }
-    for (int i = tid; i < th * bw; i += FAST_THREADS) bm[i] = 0;
+    for (int i = tid; 4 * i < th * bw; i += FAST_THREADS) ((uint4*)bm)[i] = make_uint4(0, 0, 0, 0);
     const int g0 = tc0 >> 2, g1 = (tc1 + 3) >> 2;
     // the NMS reads one word / one row beyond the scored area: only that frame has to be zero
     for (int w = g0 - 1 + tid; w <= g1; w += FAST_THREADS) {
@@ -385,16 +399,16 @@ cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cu
         maxCap = max(maxCap, g.lv[l].cellCap);
         if (g.lv[l].wCell > 64) return cudaErrorNotSupported;       // a cell's columns must fit the 64-bit row masks of phase 4
     }
-    const int need = ((maxW + 3 + 3) >> 2) + 2;        // + alignment slack + one spare word on each side
-    const int PW = need <= 81 ? 81 : 135;              // odd pitches: rows start in different banks
-    if (need > 135) return cudaErrorNotSupported;
+    const int need = ((maxW + 16) >> 2) + 4;           // + alignment slack (tile byte 0 sits on a 16-byte boundary) + whole 16-byte chunks
+    const int PW = need <= 72 ? 72 : (need <= 88 ? 88 : 136);      // multiples of 4: tile rows are 16-byte aligned in shared memory
+    if (need > 136) return cudaErrorNotSupported;
     P.pitchW = PW;
     P.tileRows = maxH;
     P.bmWords = (PW + 7) / 8 + 2;
     P.listStride = (maxCap + 1) & ~1;
     if ((size_t)2 * P.listStride * (FAST_THREADS / 32) > (size_t)4 * PW * P.tileRows) return cudaErrorNotSupported;
-    size_t smem = (size_t)4 * (PW * (3 * P.tileRows + 6) + P.tileRows * P.bmWords) + 16;
+    size_t smem = (size_t)4 * (((PW * (3 * P.tileRows + 6) + 3) & ~3) + ((P.tileRows * P.bmWords + 3) & ~3)) + 16;
     if (smem > 200 * 1024) return cudaErrorNotSupported;
     dim3 grid(g.groupsPerFrame, nframes);
-    return PW == 81 ? launch_fast_pw<81>(P, smem, grid, s) : launch_fast_pw<135>(P, smem, grid, s);
+    return PW == 72 ? launch_fast_pw<72>(P, smem, grid, s) : (PW == 88 ? launch_fast_pw<88>(P, smem, grid, s) : launch_fast_pw<136>(P, smem, grid, s));
 }
