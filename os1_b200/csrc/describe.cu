@@ -20,6 +20,7 @@
 #define RAW_PW 13         // window row pitch in words (52 bytes >= 3 + 43, odd)
 #define HB_W 37           // blurred window side
 #define HB_Q 10           // groups of four blurred columns
+#define HB_PAIRS 22       // pairs of window rows (43 rows; the last pair's second row is padding)
 #define BL_PITCH 40
 
 namespace {
@@ -42,8 +43,21 @@ struct DescParams {
 struct WarpSmem {
     unsigned raw[WIN * RAW_PW];         // source window as fetched: window column c sits at byte c + shift;
                                         // after the horizontal pass the same words hold the blurred 37x37 window (bytes)
-    uint2 hb[WIN * HB_Q];               // horizontal pass, per row and group of four: {(H0,H2), (H1,H3)} as u16x2
+    uint4 hp[HB_PAIRS * HB_Q];          // horizontal pass, per PAIR of rows (2e, 2e+1) and group of four columns:
+                                        // four u16x2 words {H[2e][j] | H[2e+1][j] << 16}, j = 4q .. 4q+3
 };
+
+// Intensity-centroid coefficients, one row of the 31x31 patch per lane: for |v| = 0..15 and the nine aligned words that
+// hold patch columns 4..39 of the window, the signed column offsets u (0 outside the circle) and the 0/1 membership
+// mask (ORBextractor.cc:86-113 with umax of :486-501).  Built once per CTA from umax.
+struct IcTab { int cu[16][9]; unsigned cm[16][9]; };
+
+__device__ __forceinline__ int dp4a_us(unsigned a, int b, int c)
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 __device__ __forceinline__ int reflect101(int p, int len)
 {
@@ -70,15 +84,20 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x, const DescPara
     return a;
 }
 
-// one output of the vertical 7-tap pass: (sum k_j * H_j + 32768) >> 16 with k = {18,34,48,56,48,34,18}
-__device__ __forceinline__ unsigned vtap(int r0, int r1, int r2, int r3, int r4, int r5, int r6)
-{
-    return (unsigned)((18 * (r0 + r6) + 34 * (r1 + r5) + 48 * (r2 + r4) + 56 * r3 + 32768) >> 16);
-}
-
 __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __grid_constant__ DescParams P)
 {
     __shared__ WarpSmem sm[DESC_WARPS];
+    __shared__ IcTab ic;
+    for (int i = threadIdx.x; i < 16 * 9; i += DESC_WARPS * 32) {
+        const int av = i / 9, k = i - av * 9;
+        int cu = 0; unsigned cm = 0;
+        for (int b = 0; b < 4; b++) {
+            const int u = 4 * (k + 1) + b - WIN_R;                   // window column 4(k+1)+b  <->  patch offset u
+            if (u >= -P.umax[av] && u <= P.umax[av]) { cu |= (u & 0xFF) << (8 * b); cm |= 1u << (8 * b); }
+        }
+        ic.cu[av][k] = cu; ic.cm[av][k] = cm;
+    }
+    __syncthreads();
     const Geometry& g = P.g;
     const int frame = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -134,77 +153,87 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __gr
     }
     __syncwarp();
 
-    // ---- intensity centroid (lanes = columns u, loop over rows v) ----------------------------------------------
+    // ---- intensity centroid: lane = patch row v.  The row's 31 pixels sit in nine aligned words; one dp4a per word
+    // against the signed column offsets gives sum(u * I), one against the membership mask gives sum(I). -----------------
     int m10 = 0, m01 = 0;
-    {
-        const int u = lane - 15;
-        if (lane < 31) {
-            const int au = u < 0 ? -u : u;
-            const uint8_t* col = (const uint8_t*)S.raw + WIN_R + u + sh;
-#pragma unroll 1
-            for (int vv = -15; vv <= 15; vv++) {
-                const int av = vv < 0 ? -vv : vv;
-                if (au <= P.umax[av]) {
-                    const int val = col[(WIN_R + vv) * (RAW_PW * 4)];
-                    m10 += u * val;
-                    m01 += vv * val;
-                }
-            }
-        }
+    const int s8 = 8 * sh;
+    if (lane < 31) {
+        const int vv = lane - 15, av = vv < 0 ? -vv : vv;
+        const unsigned* w = S.raw + (WIN_R + vv) * RAW_PW + 1;
+        unsigned prev = w[0];
+        int rowSum = 0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        for (int k = 0; k < 9; k++) {
+            const unsigned next = w[k + 1];
+            const unsigned a = __funnelshift_r(prev, next, s8);         // window columns 4(k+1) .. 4(k+1)+3
+            prev = next;
+            m10 = dp4a_us(a, ic.cu[av][k], m10);
+            rowSum = (int)__dp4a(a, ic.cm[av][k], (unsigned)rowSum);
         }
+        m01 = vv * rowSum;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
     }
     const float angle = fast_atan2_deg((float)m01, (float)m10, P);
 
     // ---- 7x7 Gaussian, Q8 taps {18,34,48,56,48,34,18}, exact two-pass fixed point ----------------------------------
-    // Horizontal pass, four outputs per item on packed u16x2 arithmetic (an output is <= 65280, so two of them share
-    // a 32-bit multiply-add without carries): pair E = outputs (0,2) of the group, pair O = outputs (1,3);
-    // tap i of E is the byte pair (i, i+2) of the aligned 12-byte block, tap i of O is byte pair (i+1, i+3).
+    // Horizontal pass: item = (pair of rows, group of four columns).  After aligning the row to the window's byte phase,
+    // output x of the group is dp4a(bytes x..x+3, {18,34,48,56}) + dp4a(bytes x+4..x+7, {48,34,18,0}); the results of the
+    // two rows (<= 65280 each) are packed as u16x2 so that the vertical pass can use dp2a on them.
     {
-        const int s8 = 8 * sh;
-        for (int it = lane; it < WIN * HB_Q; it += 32) {
-            const int r = (it * 6554) >> 16;            // it / 10
-            const int q = it - r * HB_Q;
-            const unsigned* w = S.raw + r * RAW_PW + q;
-            const unsigned W0 = w[0], W1 = w[1], W2 = w[2], W3 = w[3];
-            const unsigned A0 = __funnelshift_r(W0, W1, s8), A1 = __funnelshift_r(W1, W2, s8), A2 = __funnelshift_r(W2, W3, s8);
-            const unsigned M = 0x00FF00FFu;
-            const unsigned p0 = A0 & M, p1 = (A0 >> 8) & M, p2 = __funnelshift_r(A0, A1, 16) & M, p3 = __funnelshift_r(A0, A1, 24) & M;
-            const unsigned p4 = A1 & M, p5 = (A1 >> 8) & M, p6 = __funnelshift_r(A1, A2, 16) & M, p7 = __funnelshift_r(A1, A2, 24) & M;
-            uint2 o;
-            o.x = 18u * (p0 + p6) + 34u * (p1 + p5) + 48u * (p2 + p4) + 56u * p3;
-            o.y = 18u * (p1 + p7) + 34u * (p2 + p6) + 48u * (p3 + p5) + 56u * p4;
-            S.hb[r * HB_Q + q] = o;
+        const unsigned K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K2 = 48u | (34u << 8) | (18u << 16);
+        for (int it = lane; it < HB_PAIRS * HB_Q; it += 32) {
+            const int e = (it * 6554) >> 16;            // it / 10
+            const int q = it - e * HB_Q;
+            unsigned h[2][4];
+#pragma unroll
+            for (int rr = 0; rr < 2; rr++) {
+                const int r = min(2 * e + rr, WIN - 1);
+                const unsigned* w = S.raw + r * RAW_PW + q;
+                const unsigned W0 = w[0], W1 = w[1], W2 = w[2], W3 = w[3];
+                const unsigned A0 = __funnelshift_r(W0, W1, s8), A1 = __funnelshift_r(W1, W2, s8), A2 = __funnelshift_r(W2, W3, s8);
+                h[rr][0] = __dp4a(A0, K1, __dp4a(A1, K2, 0u));
+                h[rr][1] = __dp4a(__funnelshift_r(A0, A1, 8), K1, __dp4a(__funnelshift_r(A1, A2, 8), K2, 0u));
+                h[rr][2] = __dp4a(__funnelshift_r(A0, A1, 16), K1, __dp4a(__funnelshift_r(A1, A2, 16), K2, 0u));
+                h[rr][3] = __dp4a(__funnelshift_r(A0, A1, 24), K1, __dp4a(__funnelshift_r(A1, A2, 24), K2, 0u));
+            }
+            S.hp[it] = make_uint4(h[0][0] | (h[1][0] << 16), h[0][1] | (h[1][1] << 16), h[0][2] | (h[1][2] << 16), h[0][3] | (h[1][3] << 16));
         }
     }
     __syncwarp();
     unsigned* bl = S.raw;               // the raw window is dead from here on (37 * 10 words <= 43 * 13)
-    // Vertical pass: lane = (group of four columns, third of the rows); a 7-row window of unpacked sums slides down.
+    // Vertical pass: lane = (group of four columns, third of the rows).  Output rows 2m and 2m+1 both read the row pairs
+    // m .. m+3 — with taps {k0,k1 | k2,k3 | k4,k5 | k6,0} and {0,k0 | k1,k2 | k3,k4 | k5,k6} — so a four-pair window
+    // slides down one pair per step, and an output is four dp2a starting from the rounding constant.
     if (lane < 3 * HB_Q) {
         const int seg = lane / HB_Q, q = lane - seg * HB_Q;
-        const int rb = seg == 0 ? 0 : (seg == 1 ? 13 : 25), re = seg == 0 ? 13 : (seg == 1 ? 25 : 37);
-        int wnd[7][4];                                  // circular: step t keeps rows rb+t .. rb+t+6 in slots (t+j) % 7
+        const int mb = seg == 0 ? 0 : (seg == 1 ? 7 : 13), me = seg == 0 ? 7 : (seg == 1 ? 13 : 19);
+        const unsigned CE = 18u | (34u << 8) | (48u << 16) | (56u << 24), CE2 = 48u | (34u << 8) | (18u << 16);
+        const unsigned CO = (18u << 8) | (34u << 16) | (48u << 24), CO2 = 56u | (48u << 8) | (34u << 16) | (18u << 24);
+        uint4 wnd[4];                                   // circular: step t keeps pairs mb+t .. mb+t+3 in slots (t+j) % 4
 #pragma unroll
-        for (int k = 0; k < 6; k++) {
-            const uint2 hh = S.hb[(rb + k) * HB_Q + q];
-            wnd[k][0] = hh.x & 0xFFFF; wnd[k][2] = hh.x >> 16; wnd[k][1] = hh.y & 0xFFFF; wnd[k][3] = hh.y >> 16;
-        }
+        for (int k = 0; k < 3; k++) wnd[k] = S.hp[(mb + k) * HB_Q + q];
 #pragma unroll
-        for (int t = 0; t < 13; t++) {
-            const int r = rb + t;
-            if (r < re) {
-                const uint2 hh = S.hb[(r + 6) * HB_Q + q];
-                const int n = (t + 6) % 7;
-                wnd[n][0] = hh.x & 0xFFFF; wnd[n][2] = hh.x >> 16; wnd[n][1] = hh.y & 0xFFFF; wnd[n][3] = hh.y >> 16;
-                unsigned o = 0;
+        for (int t = 0; t < 7; t++) {
+            const int m = mb + t;
+            if (m < me) {
+                wnd[(t + 3) % 4] = S.hp[(m + 3) * HB_Q + q];
+                const uint4 p0 = wnd[t % 4], p1 = wnd[(t + 1) % 4], p2 = wnd[(t + 2) % 4], p3 = wnd[(t + 3) % 4];
+                const unsigned a0[4] = { p0.x, p0.y, p0.z, p0.w }, a1[4] = { p1.x, p1.y, p1.z, p1.w };
+                const unsigned a2[4] = { p2.x, p2.y, p2.z, p2.w }, a3[4] = { p3.x, p3.y, p3.z, p3.w };
+                unsigned ev[4], od[4];
 #pragma unroll
-                for (int c = 0; c < 4; c++)
-                    o |= vtap(wnd[t % 7][c], wnd[(t + 1) % 7][c], wnd[(t + 2) % 7][c], wnd[(t + 3) % 7][c], wnd[(t + 4) % 7][c],
-                              wnd[(t + 5) % 7][c], wnd[(t + 6) % 7][c]) << (8 * c);
-                bl[r * (BL_PITCH / 4) + q] = o;
+                for (int c = 0; c < 4; c++) {
+                    ev[c] = __dp2a_hi(a3[c], CE2, __dp2a_lo(a2[c], CE2, __dp2a_hi(a1[c], CE, __dp2a_lo(a0[c], CE, 32768u))));
+                    od[c] = __dp2a_hi(a3[c], CO2, __dp2a_lo(a2[c], CO2, __dp2a_hi(a1[c], CO, __dp2a_lo(a0[c], CO, 32768u))));
+                }
+                // (sum + 32768) >> 16 is byte 2 of each accumulator (< 2^24)
+                bl[(2 * m) * (BL_PITCH / 4) + q] = __byte_perm(__byte_perm(ev[0], ev[1], 0x0062), __byte_perm(ev[2], ev[3], 0x0062), 0x5410);
+                if (2 * m + 1 < HB_W)
+                    bl[(2 * m + 1) * (BL_PITCH / 4) + q] = __byte_perm(__byte_perm(od[0], od[1], 0x0062), __byte_perm(od[2], od[3], 0x0062), 0x5410);
             }
         }
     }
