@@ -241,7 +241,9 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __gr
 
     // ---- rotated BRIEF: lane = descriptor byte ---------------------------------------------------------------------------
     const float ang = __fmul_rn(angle, P.factorPI);
-    const float a = (float)cos((double)ang), b = (float)sin((double)ang);
+    double sd, cd;
+    sincos((double)ang, &sd, &cd);             // one range reduction for both
+    const float a = (float)cd, b = (float)sd;
     const int4* pat = (const int4*)d_pattern;
     int4 w0 = __ldg(pat + 2 * lane), w1 = __ldg(pat + 2 * lane + 1);
     const int words[8] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w };
