@@ -17,7 +17,8 @@
 #define DESC_WARPS 4
 #define WIN 43            // 2*(18+3)+1 : rotated pattern reach 18 (|p| <= 18.38) + blur radius 3
 #define WIN_R 21
-#define RAW_PW 13         // window row pitch in words (52 bytes >= 3 + 43, odd)
+#define RAW_PW 20         // window row pitch in words: four 16-byte chunks hold the 43 bytes wherever they start, and a fifth
+                          // of padding spreads the rows over the banks (pitch 16 would put every row pair on the same ones)
 #define HB_W 37           // blurred window side
 #define HB_Q 10           // groups of four blurred columns
 #define HB_PAIRS 22       // pairs of window rows (43 rows; the last pair's second row is padding)
@@ -41,7 +42,7 @@ struct DescParams {
 };
 
 struct WarpSmem {
-    unsigned raw[WIN * RAW_PW];         // source window as fetched: window column c sits at byte c + shift;
+    uint4 raw4[WIN * RAW_PW / 4];       // source window as fetched: window column c sits at byte c + shift (< 16);
                                         // after the horizontal pass the same words hold the blurred 37x37 window (bytes)
     uint4 hp[HB_PAIRS * HB_Q];          // horizontal pass, per PAIR of rows (2e, 2e+1) and group of four columns:
                                         // four u16x2 words {H[2e][j] | H[2e+1][j] << 16}, j = 4q .. 4q+3
@@ -49,8 +50,9 @@ struct WarpSmem {
 
 // Intensity-centroid coefficients, one row of the 31x31 patch per lane: for |v| = 0..15 and the nine aligned words that
 // hold patch columns 4..39 of the window, the signed column offsets u (0 outside the circle) and the 0/1 membership
-// mask (ORBextractor.cc:86-113 with umax of :486-501).  Built once per CTA from umax.
+// mask (ORBextractor.cc:86-113 with umax of :486-501).  Filled by the launcher once per device.
 struct IcTab { int cu[16][9]; unsigned cm[16][9]; };
+__device__ IcTab d_ic;
 
 __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c)
 {
@@ -84,19 +86,11 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x, const DescPara
     return a;
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __grid_constant__ DescParams P)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 8) describe_kernel(const __grid_constant__ DescParams P)
 {
     __shared__ WarpSmem sm[DESC_WARPS];
     __shared__ IcTab ic;
-    for (int i = threadIdx.x; i < 16 * 9; i += DESC_WARPS * 32) {
-        const int av = i / 9, k = i - av * 9;
-        int cu = 0; unsigned cm = 0;
-        for (int b = 0; b < 4; b++) {
-            const int u = 4 * (k + 1) + b - WIN_R;                   // window column 4(k+1)+b  <->  patch offset u
-            if (u >= -P.umax[av] && u <= P.umax[av]) { cu |= (u & 0xFF) << (8 * b); cm |= 1u << (8 * b); }
-        }
-        ic.cu[av][k] = cu; ic.cm[av][k] = cm;
-    }
+    for (int i = threadIdx.x; i < (int)(sizeof(IcTab) / 4); i += DESC_WARPS * 32) ((unsigned*)&ic)[i] = __ldg((const unsigned*)&d_ic + i);
     __syncthreads();
     const Geometry& g = P.g;
     const int frame = blockIdx.y;
@@ -104,13 +98,18 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __gr
     const int slot = blockIdx.x * DESC_WARPS + warp;
 
     // level of this slot from the per-level kept counts (:936-967 concatenates levels in order)
-    const uint32_t* lvCount = P.d.lvCount + frame * g.nlevels;
-    int level = -1, j = slot, total = 0;
-    for (int l = 0; l < g.nlevels; l++) {
-        const int c = (int)lvCount[l];
-        if (level < 0 && slot - total < c) { level = l; j = slot - total; }
-        total += c;
+    // (lane l holds level l's count; an inclusive scan over the first 16 lanes gives every level's end slot)
+    const int cnt = lane < g.nlevels ? (int)P.d.lvCount[frame * g.nlevels + lane] : 0;
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 16; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
     }
+    const int total = __shfl_sync(0xffffffffu, incl, OS1_MAX_LEVELS - 1);
+    const int below = __popc(__ballot_sync(0xffffffffu, lane < g.nlevels && incl <= slot));     // levels that end at or before the slot
+    const int level = below < g.nlevels ? below : -1;
+    const int j = slot - __shfl_sync(0xffffffffu, incl - cnt, below & 31);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         P.counts[frame] = min(total, P.capPerFrame);
         if (total > P.capPerFrame) atomicOr(P.d.status, OS1_ERR_KP_OVERFLOW);
@@ -126,25 +125,26 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __gr
     else { img = P.d.slab + (long long)frame * g.slabBytes + L.off; pitch = L.pitch; }
 
     WarpSmem& S = sm[warp];
-    // ---- 43x43 window -> shared.  Interior keypoints: aligned 32-bit loads of the rows (12 words cover the 43 bytes
-    // wherever they start); the window keeps the byte phase `sh` of its first column.  Keypoints within 21 px of the
-    // level's edge take the byte path with REFLECT_101 indices, as the blur of the borderless clone sees them. ----------
+    // ---- 43x43 window -> shared.  Interior keypoints: 16-byte asynchronous copies of the rows, starting at the 16-byte
+    // boundary at or before the window's first column (level rows start aligned and have a pitch that is a multiple of
+    // 16); the window keeps the byte phase `sh` (< 16) of its first column.  Keypoints within 21 px of the level's edge
+    // take the byte path with REFLECT_101 indices, as the blur of the borderless clone sees them — and so do the few
+    // whose last chunk would end beyond the bytes the level owns. ----------------------------------------------------
     const int xs = x - WIN_R, ys = y - WIN_R;
-    int sh;
-    if (xs >= 0 && ys >= 0 && x + WIN_R < L.w && y + WIN_R < L.h) {
-        sh = xs & 3;
+    int sh = xs & 15;
+    const int nch = (sh + WIN + 15) >> 4;                       // chunks that hold window bytes: 3 or 4
+    if (xs >= 0 && ys >= 0 && x + WIN_R < L.w && y + WIN_R < L.h && xs - sh + 16 * nch <= (level == 0 ? L.w : pitch)) {
         const uint8_t* base = img + (long long)ys * pitch + (xs - sh);
-        for (int it = lane; it < WIN * 12; it += 32) {
-            const int r = (it * 5462) >> 16;            // it / 12
-            const int w = it - r * 12;
-            if (4 * w <= sh + WIN - 1)                  // never touch a word that holds no window byte (row end)
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(S.raw + r * RAW_PW + w)),
-                             "l"(base + (long long)r * pitch + 4 * w) : "memory");      // all 17 copies of a lane in flight at once
+        for (int it = lane; it < WIN * 4; it += 32) {
+            const int r = it >> 2, c = it & 3;
+            if (c < nch)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(S.raw4 + r * (RAW_PW / 4) + c)),
+                             "l"(base + (long long)r * pitch + 16 * c) : "memory");      // all 6 copies of a lane in flight at once
         }
         asm volatile("cp.async.wait_all;" ::: "memory");
     } else {
         sh = 0;
-        uint8_t* rb = (uint8_t*)S.raw;
+        uint8_t* rb = (uint8_t*)S.raw4;
         for (int i = lane; i < WIN * WIN; i += 32) {
             const int r = i / WIN, c = i - r * WIN;
             const int yy = reflect101(ys + r, L.h), xx = reflect101(xs + c, L.w);
@@ -152,21 +152,23 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __gr
         }
     }
     __syncwarp();
+    const unsigned* raw = (const unsigned*)S.raw4 + (sh >> 2);   // word that holds window column 0
+    const int s8 = 8 * (sh & 3);
 
     // ---- intensity centroid: lane = patch row v.  The row's 31 pixels sit in nine aligned words; one dp4a per word
     // against the signed column offsets gives sum(u * I), one against the membership mask gives sum(I). -----------------
     int m10 = 0, m01 = 0;
-    const int s8 = 8 * sh;
     if (lane < 31) {
         const int vv = lane - 15, av = vv < 0 ? -vv : vv;
-        const unsigned* w = S.raw + (WIN_R + vv) * RAW_PW + 1;
-        unsigned prev = w[0];
+        const unsigned* w = raw + (WIN_R + vv) * RAW_PW + 1;
+        // (rows 8 apart start in the same bank: each lane walks its nine words from a different one)
+        const int rot = lane >> 3;
         int rowSum = 0;
 #pragma unroll
-        for (int k = 0; k < 9; k++) {
-            const unsigned next = w[k + 1];
-            const unsigned a = __funnelshift_r(prev, next, s8);         // window columns 4(k+1) .. 4(k+1)+3
-            prev = next;
+        for (int t = 0; t < 9; t++) {
+            int k = t + rot;
+            if (k >= 9) k -= 9;
+            const unsigned a = __funnelshift_r(w[k], w[k + 1], s8);     // window columns 4(k+1) .. 4(k+1)+3
             m10 = dp4a_us(a, ic.cu[av][k], m10);
             rowSum = (int)__dp4a(a, ic.cm[av][k], (unsigned)rowSum);
         }
@@ -192,7 +194,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __gr
 #pragma unroll
             for (int rr = 0; rr < 2; rr++) {
                 const int r = min(2 * e + rr, WIN - 1);
-                const unsigned* w = S.raw + r * RAW_PW + q;
+                const unsigned* w = raw + r * RAW_PW + q;
                 const unsigned W0 = w[0], W1 = w[1], W2 = w[2], W3 = w[3];
                 const unsigned A0 = __funnelshift_r(W0, W1, s8), A1 = __funnelshift_r(W1, W2, s8), A2 = __funnelshift_r(W2, W3, s8);
                 h[rr][0] = __dp4a(A0, K1, __dp4a(A1, K2, 0u));
@@ -204,7 +206,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __gr
         }
     }
     __syncwarp();
-    unsigned* bl = S.raw;               // the raw window is dead from here on (37 * 10 words <= 43 * 13)
+    unsigned* bl = (unsigned*)S.raw4;   // the raw window is dead from here on (37 * 10 words <= 43 * 20)
     // Vertical pass: lane = (group of four columns, third of the rows).  Output rows 2m and 2m+1 both read the row pairs
     // m .. m+3 — with taps {k0,k1 | k2,k3 | k4,k5 | k6,0} and {0,k0 | k1,k2 | k3,k4 | k5,k6} — so a four-pair window
     // slides down one pair per step, and an output is four dp2a starting from the rounding constant.
@@ -291,6 +293,28 @@ cudaError_t os1_launch_describe(const Geometry& g, const DevPtrs& d, int nframes
             while (P.umax[v0] == P.umax[v0 + 1]) ++v0;
             P.umax[v] = v0;
             ++v0;
+        }
+    }
+    {
+        static bool filled[64] = { false };
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !filled[dev]) {
+            IcTab t;
+            for (int av = 0; av < 16; av++)
+                for (int k = 0; k < 9; k++) {
+                    int cu = 0; unsigned cm = 0;
+                    for (int b = 0; b < 4; b++) {
+                        const int u = 4 * (k + 1) + b - WIN_R;               // window column 4(k+1)+b  <->  patch offset u
+                        if (u >= -P.umax[av] && u <= P.umax[av]) { cu |= (u & 0xFF) << (8 * b); cm |= 1u << (8 * b); }
+                    }
+                    t.cu[av][k] = cu; t.cm[av][k] = cm;
+                }
+            cudaError_t e = cudaMemcpyToSymbolAsync(d_ic, &t, sizeof(t), 0, cudaMemcpyHostToDevice, s);
+            if (e != cudaSuccess) return e;
+            e = cudaStreamSynchronize(s);            // `t` lives on this stack frame
+            if (e != cudaSuccess) return e;
+            filled[dev] = true;
         }
     }
     volatile float R = (float)(180.0 / 3.1415926535897932384626433832795);
