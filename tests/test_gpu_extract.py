@@ -77,6 +77,9 @@ def test_against_committed_reference_golden(golden_dir, name):
     ((480, 640), 250, 1.2, 8, 40, 12, 7),       # other thresholds, few features
     ((360, 1000), 800, 1.2, 5, 20, 7, 8),       # 3 quadtree roots
     ((480, 640), 3000, 1.2, 8, 20, 7, 9),       # more features than good candidates in the small levels
+    ((85, 85), 60, 1.2, 1, 20, 7, 11),          # one FAST cell of 59 x 59: the widest and tallest a cell can be
+    ((80, 100), 100, 1.2, 2, 20, 7, 12),        # cells wider than 32 columns, one cell row taller than 32
+    ((220, 800), 400, 1.2, 3, 20, 7, 13),       # four quadtree roots (the widest aspect supported)
 ])
 def test_other_geometries(oracle_lib, shape, nf, sf, nl, ini, mn, seed):
     compare_full(oracle_lib, synth.frame(shape[0], shape[1], seed), nf, sf, nl, ini, mn)
