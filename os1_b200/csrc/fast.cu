@@ -47,6 +47,7 @@ struct FastParams {
     int tileRows;
     int bmWords;        // words per row of the survivor bitmap (one bit per tile byte column, + 2 spare)
     int listStride;     // u16 slots per warp for the survivor list of a cell (aliases the image tile)
+    int qStride;        // u16 slots per warp for the queue of groups that pass the compass test
 };
 
 // ---- packed ring access -------------------------------------------------------------------------------------
@@ -182,6 +183,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
         const int nch = (words + 3) >> 2;                   // 16-byte chunks per tile row
         const unsigned rcpCh = c_rcp.v[nch];
         const int lw = L.w;
+#pragma unroll 1
         for (int i = tid; i < th * nch; i += FAST_THREADS) {
             const int r = (int)(((unsigned)i * rcpCh) >> 24), c = i - r * nch;
             const uint8_t* gsrc = src + (long long)(y0 + r) * spitch + xorg + 16 * c;
@@ -197,6 +199,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     }
     // ---- phase 0/1: lane masks, tile -> shared, cleared score-map frame and bitmap ------------------------------------
     const unsigned rcpW = c_rcp.v[wCell];
+#pragma unroll 1
     for (int w = tid; w < pw; w += FAST_THREADS) {
         unsigned vm[4], lm[4], rm[4];
 #pragma unroll
@@ -213,13 +216,16 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
         lmE[w] = lm[0] | (lm[2] << 16); lmO[w] = lm[1] | (lm[3] << 16);
         rmE[w] = rm[0] | (rm[2] << 16); rmO[w] = rm[1] | (rm[3] << 16);
     }
+#pragma unroll 1
     for (int i = tid; 4 * i < th * bw; i += FAST_THREADS) ((uint4*)bm)[i] = make_uint4(0, 0, 0, 0);
     const int g0 = tc0 >> 2, g1 = (tc1 + 3) >> 2;
     // the NMS reads one word / one row beyond the scored area: only that frame has to be zero
+#pragma unroll 1
     for (int w = g0 - 1 + tid; w <= g1; w += FAST_THREADS) {
         scE[(tr0 - 1) * pw + w] = 0; scO[(tr0 - 1) * pw + w] = 0;
         scE[tr1 * pw + w] = 0; scO[tr1 * pw + w] = 0;
     }
+#pragma unroll 1
     for (int r = tr0 + tid; r < tr1; r += FAST_THREADS) {
         scE[r * pw + g0 - 1] = 0; scO[r * pw + g0 - 1] = 0;
         scE[r * pw + g1] = 0; scO[r * pw + g1] = 0;
@@ -232,11 +238,54 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     // stored s8 = strength - tmin; response = strength - 1 = s8 + tmin - 1
     const int iniS8 = g.iniTh - tmin + 1, minS8 = g.minTh - tmin + 1;
     // ---- phase 2: scores, four pixels per thread, kept packed ---------------------------------------------------------
+    // (rows x groups flattened so that every lane has work: 75 groups per row would leave a third of the lanes idle in
+    //  the last of three 32-wide trips; the division by the group count is a multiply by its reciprocal)
     {
         const unsigned T = (unsigned)tmin * 0x01000100u;       // tmin << 8 in both lanes
-        // (rows x groups flattened so that every lane has work: 75 groups per row would leave a third of the lanes
-        //  idle in the last of three 32-wide trips; the division by the group count is a multiply by its reciprocal)
-        for (int idx = tid; idx < nItems; idx += FAST_THREADS) {
+        // 2a: a necessary condition from the four compass points of the ring.  An arc of 9 contains two ADJACENT compass
+        // points, so  max over adjacent pairs of min(pair) >= darkest  and  min over pairs of max(pair) <= brightest:
+        // if that bound does not exceed tmin, the group's four scores are zero.  Groups that pass are queued (per warp,
+        // ballot-compacted) and scored in full by the same warp in 2b, all lanes busy.
+        const unsigned T1 = (unsigned)((tmin + 1) * 256 - 1) * 0x00010001u;
+        unsigned short* queue = (unsigned short*)(bm + ((th * bw + 3) & ~3)) + warp * P.qStride;
+        int qn = 0;
+        const unsigned ltmask = (1u << lane) - 1u;
+#pragma unroll 1
+        for (int idx0 = warp * 32; idx0 < nItems; idx0 += FAST_THREADS) {
+            const int idx = idx0 + lane;
+            bool pass = false;
+            if (idx < nItems) {
+                const int rr = (int)(((unsigned)idx * rcpNg) >> 24);
+                const int r = tr0 + rr, gq = g0 + idx - rr * ng;
+                const unsigned* row = img + r * pw + gq;
+                const unsigned tm = row[-3 * pw - 1], t0 = row[-3 * pw], tp = row[-3 * pw + 1];      // ring 8: (0,-3)
+                const unsigned cm = row[-1], c0 = row[0], cp = row[1];                                 // ring 4: (3,0), 12: (-3,0)
+                const unsigned bmw_ = row[3 * pw - 1], b0 = row[3 * pw], bp = row[3 * pw + 1];       // ring 0: (0,3)
+                const unsigned cE = __byte_perm(c0, 0, 0x2404), cO = __byte_perm(c0, 0, 0x3414);
+                unsigned u[2];
+#pragma unroll
+                for (int odd = 0; odd < 2; odd++) {
+                    const unsigned r0 = odd ? ring_pair<0, 1>(bmw_, b0, bp) : ring_pair<0, 0>(bmw_, b0, bp);
+                    const unsigned r4 = odd ? ring_pair<3, 1>(cm, c0, cp) : ring_pair<3, 0>(cm, c0, cp);
+                    const unsigned r8 = odd ? ring_pair<0, 1>(tm, t0, tp) : ring_pair<0, 0>(tm, t0, tp);
+                    const unsigned r12 = odd ? ring_pair<-3, 1>(cm, c0, cp) : ring_pair<-3, 0>(cm, c0, cp);
+                    const unsigned c = odd ? cO : cE;
+                    const unsigned lo = __vmaxu2(__vimax3_u16x2(__vminu2(r0, r4), __vminu2(r4, r8), __vminu2(r8, r12)), __vminu2(r12, r0));
+                    const unsigned hi = __vminu2(__vimin3_u16x2(__vmaxu2(r0, r4), __vmaxu2(r4, r8), __vmaxu2(r8, r12)), __vmaxu2(r12, r0));
+                    u[odd] = __vmaxu2(usubsat2(lo, c), usubsat2(c | 0x00FF00FFu, hi));
+                }
+                pass = (usubsat2(u[0], T1) | usubsat2(u[1], T1)) != 0;
+                if (!pass) { scE[r * pw + gq] = 0; scO[r * pw + gq] = 0; }
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, pass);
+            if (pass) queue[qn + __popc(bal & ltmask)] = (unsigned short)idx;
+            qn += __popc(bal);
+        }
+        __syncwarp();
+        // 2b: the full score of the queued groups
+#pragma unroll 1
+        for (int i = lane; i < qn; i += 32) {
+                const int idx = queue[i];
                 const int rr = (int)(((unsigned)idx * rcpNg) >> 24);
                 const int r = tr0 + rr, gq = g0 + idx - rr * ng;
                 unsigned W[7][3];
@@ -258,7 +307,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
                 const unsigned sO = __vmaxu2(usubsat2(dO, cO), usubsat2(cOf, bO));
                 scE[r * pw + gq] = usubsat2(sE, T) & vmE[gq];        // (the masks also clear the low bytes)
                 scO[r * pw + gq] = usubsat2(sO, T) & vmO[gq];
-            }
+        }
     }
     __syncthreads();
 
@@ -316,6 +365,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
     // the survivors, in row-major order (cv::FAST's), to a list in the dead image tile.  Pass B, lanes = survivors: vote
     // "any survivor >= iniTh", keep those or else the ones >= minTh (the reference's retry with minThFAST,
     // ORBextractor.cc:852-856) and emit them at their rank among the kept ones. -------------------------------------
+#pragma unroll 1
     for (int cc = warp; cc < ncell; cc += FAST_THREADS / 32) {
         const int cx0 = tc0 + cc * wCell, cx1 = min(cx0 + wCell, tc1);      // tile byte columns of the cell (at most 64)
         const int wsel = cx0 >> 5, bsh = cx0 & 31, width = cx1 - cx0;
@@ -324,6 +374,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
         uint32_t* out = P.d.stage + (long long)frame * g.candPerFrame + L.candOff + (long long)(ci * L.nCols + j0 + cc) * L.cellCap;
         unsigned short* list = (unsigned short*)img + warp * P.listStride;      // entries: row << 6 | column inside the cell
         int n = 0;
+#pragma unroll 1
         for (int r0 = tr0; r0 < tr1; r0 += 32) {                                // (cells taller than 32 tested rows: two trips)
             const int r = r0 + lane;
             unsigned lo = 0, hi = 0;
@@ -355,9 +406,11 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_cons
         };
         unsigned e = 0; int s8 = 0;
         bool st = false;
+#pragma unroll 1
         for (int i = lane; i < n; i += 32) { e = list[i]; s8 = score8(e); st = st || s8 >= iniS8; }
         const int lim = __any_sync(0xffffffffu, st) ? iniS8 : minS8;
         int base = 0;
+#pragma unroll 1
         for (int i0 = 0; i0 < n; i0 += 32) {
             const int i = i0 + lane;
             if (n > 32 && i < n) { e = list[i]; s8 = score8(e); }       // up to 32 survivors: the vote's registers are this trip's
@@ -406,8 +459,14 @@ cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cu
     P.tileRows = maxH;
     P.bmWords = (PW + 7) / 8 + 2;
     P.listStride = (maxCap + 1) & ~1;
+    {
+        int maxItems = 1;
+        for (int l = 0; l < g.nlevels; l++)
+            if (g.lv[l].nCells) maxItems = max(maxItems, (((FAST_G * g.lv[l].wCell + 6 + 16) >> 2) + 1) * g.lv[l].hCell);
+        P.qStride = ((maxItems + FAST_THREADS - 1) / FAST_THREADS) * 32;       // a warp sees at most every 8th trip of 32 items
+    }
     if ((size_t)2 * P.listStride * (FAST_THREADS / 32) > (size_t)4 * PW * P.tileRows) return cudaErrorNotSupported;
-    size_t smem = (size_t)4 * (((PW * (3 * P.tileRows + 6) + 3) & ~3) + ((P.tileRows * P.bmWords + 3) & ~3)) + 16;
+    size_t smem = (size_t)4 * (((PW * (3 * P.tileRows + 6) + 3) & ~3) + ((P.tileRows * P.bmWords + 3) & ~3)) + (size_t)2 * P.qStride * (FAST_THREADS / 32) + 16;
     if (smem > 200 * 1024) return cudaErrorNotSupported;
     dim3 grid(g.groupsPerFrame, nframes);
     return PW == 72 ? launch_fast_pw<72>(P, smem, grid, s) : (PW == 88 ? launch_fast_pw<88>(P, smem, grid, s) : launch_fast_pw<136>(P, smem, grid, s));
