@@ -63,8 +63,11 @@ __device__ __forceinline__ int block_scan_excl(int v, int* warpSums, int& total)
 template <int QT_THREADS>
 __device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
 {
+#pragma unroll 1
     for (int k = 2; k <= n; k <<= 1)
+#pragma unroll 1
         for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll 1
             for (int i = threadIdx.x; i < n; i += QT_THREADS) {
                 int ixj = i ^ j;
                 if (ixj > i) {
@@ -121,6 +124,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
     int n;
     {
         int carry = 0;
+#pragma unroll 1
         for (int base = 0; base < L.nCells; base += QT_THREADS) {
             int c = base + tid;
             int v = (c < L.nCells) ? (int)cellCnt[c] : 0;
@@ -135,9 +139,11 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
     __syncthreads();
 
     // ---- 1. ordered gather + path codes (warp per cell) ---------------------------------------------------------
+#pragma unroll 1
     for (int c = warp; c < L.nCells; c += QT_THREADS / 32) {
         const int off = cellOffs[c], cnt = cellOffs[c + 1] - off;
         const uint32_t* s = stage + (long long)c * L.cellCap;
+#pragma unroll 1
         for (int r = lane; r < cnt; r += 32) {
             uint32_t v = s[r];
             cand[off + r] = v;
@@ -148,8 +154,10 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
 
     // ---- 2. roots (:584-617) ----------------------------------------------------------------------------------------
     const int nIni = L.nIni;
+#pragma unroll 1
     for (int i = tid; i < 4 * P.maxNodes; i += QT_THREADS) slotCnt[i] = 0;
     __syncthreads();
+#pragma unroll 1
     for (int base = 0; base < n; base += 4 * QT_THREADS) {
         uint32_t cd[4];
 #pragma unroll
@@ -173,6 +181,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
     {
         // nIni is tiny: every thread walks the roots redundantly, thread 0 writes
         int e = 0, lc = 0;
+#pragma unroll 1
         for (int r = 0; r < nIni; r++) {
             const uint32_t c = slotCnt[r];
             if (c == 0) continue;
@@ -187,6 +196,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
         E = e; Lcount = lc;
     }
     __syncthreads();
+#pragma unroll 1
     for (int i = tid; i < n; i += QT_THREADS) {
         const uint32_t info = slotInfo[code[i] >> (2 * D)];
         if (info & QT_LEAF) { atomicMax(&leafBest[info & 0xFFFF], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i)); node[i] = QT_DONE; }
@@ -208,26 +218,31 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
         // processing order: list order in a full pass (roots ascending, afterwards newest first);
         // (size, creation rank) descending in the final phase (:716-717)
         if (phase == 1) {
+#pragma unroll 1
             for (int j = tid; j < E; j += QT_THREADS) {
                 int p = (round == 1) ? j : E - 1 - j;
                 procPos[j] = p; order[p] = j;
             }
         } else {
             int n2 = 1; while (n2 < E) n2 <<= 1;
+#pragma unroll 1
             for (int j = tid; j < n2; j += QT_THREADS)
                 sortBuf[j] = (j < E) ? (((unsigned long long)curSize[j] << 32) | ((unsigned long long)(curKey[j] & 0xFFFFu) << 16) | (unsigned)j) : 0ull;
             __syncthreads();
             bitonic_sort<QT_THREADS>(sortBuf, n2, true);
+#pragma unroll 1
             for (int p = tid; p < E; p += QT_THREADS) {
                 int j = (int)(sortBuf[p] & 0xFFFFu);
                 order[p] = j; procPos[j] = p;
             }
         }
+#pragma unroll 1
         for (int i = tid; i < 4 * E; i += QT_THREADS) slotCnt[i] = 0;
         __syncthreads();
 
         // sweep A: children sizes
         // (four candidates per thread per trip: the eight loads are in flight together — the sweeps are latency bound)
+#pragma unroll 1
         for (int base = 0; base < n; base += 4 * QT_THREADS) {
             int nd[4]; uint32_t cd[4];
 #pragma unroll
@@ -252,6 +267,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
         // non-empty / multi-key children per node, cumulated in processing order
         {
             int carryN = 0, carryM = 0;
+#pragma unroll 1
             for (int base = 0; base < E; base += QT_THREADS) {
                 const int p = base + tid;
                 int nz = 0, mz = 0;
@@ -271,6 +287,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
         __syncthreads();
         if (phase == 2) {
             // first processing position at which the node count reaches N (:762)
+#pragma unroll 1
             for (int p = tid; p < E; p += QT_THREADS) {
                 const bool here = Lcount + (int)nzCum[p + 1] - (p + 1) >= N;
                 const bool before = p > 0 && (Lcount + (int)nzCum[p] - p >= N);
@@ -287,6 +304,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
         if (!fin && newE > P.maxNodes) { fin = true; if (tid == 0) atomicOr(P.d.status, OS1_ERR_NODE_OVERFLOW); }
 
         // children of split nodes; unsplit nodes turn into leaves as they are
+#pragma unroll 1
         for (int p = tid; p < E; p += QT_THREADS) {
             const int j = order[p];
             if (p < nSplit) {
@@ -325,6 +343,7 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
         __syncthreads();
 
         // sweep B: re-label candidates / vote for the best response of finished leaves
+#pragma unroll 1
         for (int base = 0; base < n; base += 4 * QT_THREADS) {
             int nd[4]; uint32_t cd[4];
 #pragma unroll
@@ -361,11 +380,13 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
     if (s_err && tid == 0) atomicOr(P.d.status, OS1_ERR_NODE_OVERFLOW);
     {
         int n2 = 1; while (n2 < nLeaves) n2 <<= 1;
+#pragma unroll 1
         for (int j = tid; j < n2; j += QT_THREADS)
             sortBuf[j] = (j < nLeaves) ? (((unsigned long long)leafKey[j] << 32) | leafBest[j]) : ~0ull;
         __syncthreads();
         bitonic_sort<QT_THREADS>(sortBuf, n2, false);
         if (nLeaves > L.kpCap) { if (tid == 0) atomicOr(P.d.status, OS1_ERR_KP_OVERFLOW); nLeaves = L.kpCap; }
+#pragma unroll 1
         for (int j = tid; j < nLeaves; j += QT_THREADS) {
             const uint32_t best = (uint32_t)sortBuf[j];
             const int idx = 0xFFFFFF - (best & 0xFFFFFF);
