@@ -239,6 +239,37 @@ def extras(torch, os1_b200, dev):
     dpairs = float((cnt_[prs[:, 0]].astype(np.float64) * cnt_[prs[:, 1]]).sum())
     out["hamming_sweep_%d_frames" % F] = {"frame_pairs": int(len(prs)), "descriptor_pairs": dpairs, "ms": ms, "gpairs_per_s": dpairs / ms / 1e6,
                                           "gops_per_s": 24 * dpairs / ms / 1e6, "accepted_matches": int(acc.sum().item())}
+    # MapPoint::ComputeDistinctiveDescriptors for a map's worth of points in one launch (device pointers), with the
+    # reference's algorithm (oracle port, one host thread) on a bounded sample beside it
+    from os1_b200 import _lib
+    rng = np.random.default_rng(4)
+    M = 50000
+    cnt = rng.integers(2, 25, M); ptr = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32)
+    dd_h = rng.integers(0, 256, (int(ptr[-1]), 32), dtype=np.uint8)
+    dd = torch.from_numpy(dd_h).to(dev); dp = torch.from_numpy(ptr).to(dev)
+    bi = torch.empty(M, dtype=torch.int32, device=dev); bm = torch.empty_like(bi)
+    calld = lambda: _lib.check(_lib.load().os1_distinctive_descriptors(dd.data_ptr(), dp.data_ptr(), M, bi.data_ptr(), bm.data_ptr(), 1, dev.index,
+                                                                        s.cuda_stream))
+    for _ in range(3):
+        calld()
+    torch.cuda.synchronize(dev); e0.record(s)
+    for _ in range(10):
+        calld()
+    e1.record(s); torch.cuda.synchronize(dev)
+    msd = e0.elapsed_time(e1) / 10
+    dist_pairs = float((cnt.astype(np.float64) * (cnt - 1) / 2).sum())
+    rec = {"map_points": M, "observations": int(ptr[-1]), "ms_per_call": msd, "mpoints_per_s": M / msd / 1e3,
+           "note": "2..24 observations per point; the call includes its status read-back"}
+    try:
+        from oracle import pyoracle              # cpu-baseline leg: the checker's port, timed beside the GPU figure
+        Ms = 5000
+        t = time.perf_counter(); obi, _ = pyoracle.Oracle.distinctive_descriptors(dd_h[:ptr[Ms]], ptr[:Ms + 1]); dt = time.perf_counter() - t
+        rec["cpu_port_mpoints_per_s"] = Ms / dt / 1e6
+        rec["cpu_port_sample"] = "%d points, one host thread, %.3f s" % (Ms, dt)
+        rec["agrees_with_cpu_port"] = bool(np.array_equal(obi, bi[:Ms].cpu().numpy()))
+    except Exception as ex:
+        rec["cpu_port_sample"] = "unavailable: %s" % ex
+    out["distinctive_descriptors"] = rec
     return out
 
 

@@ -117,6 +117,19 @@ int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t
 int os1_hamming_window(const uint8_t* A, int nA, const uint8_t* B, int nB, const int32_t* ptr, const int32_t* cand, int32_t* best_idx,
                        int32_t* best_dist, int32_t* second_dist, int on_device, int device, void* cuda_stream);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:226-292) for npoints map points in one launch.
+ * desc: the observation descriptors of all points back to back (32 bytes each); point m owns rows ptr[m] .. ptr[m+1]
+ * in the order the reference iterates its observation map (:246-252).  For every point the N x N matrix of
+ * DescriptorDistance values, the median of each row = element int(0.5*(N-1)) of the sorted row (:277-279), and
+ *   best_idx[m]    = position (0 .. N-1, within the point's rows) of the FIRST row with the least median (:281-285),
+ *                    -1 for a point without observations (the reference returns before touching mDescriptor, :240, :253);
+ *   best_median[m] = that median (INT_MAX for an empty point); may be NULL.
+ * ptr has npoints+1 entries.  A point with more than 256 observations is rejected (OS1_E_UNSUPPORTED).
+ * on_device: all pointers are device memory of `device`; otherwise host memory.  Synchronous either way (the
+ * size check of the device variant reads one status word back). */
+int os1_distinctive_descriptors(const uint8_t* desc, const int32_t* ptr, int npoints, int32_t* best_idx, int32_t* best_median,
+                                int on_device, int device, void* cuda_stream);
+
 /* Many all-pairs scans in one launch — the cross-keyframe sweep of BASELINE.json configs[4].  DEVICE pointers.
  * desc: a slab of F descriptor sets, set f at desc + f*cap*32 with counts[f] valid rows; pairs: npairs x {i, j};
  * for every pair the rows of set i are scanned against the whole of set j exactly as os1_hamming_knn2 does.

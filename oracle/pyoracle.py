@@ -72,6 +72,7 @@ class Oracle:
             L.orc_features_in_area.argtypes = [_vp, _vp, _i, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i]
             L.orc_search_by_projection_frame.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
             L.orc_search_by_projection_points.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp]
+            L.orc_distinctive_descriptors.argtypes = [_vp, _vp, _i, _vp, _vp]
             cls._lib = L
         return cls._lib
 
@@ -214,6 +215,15 @@ class Oracle:
         tot = cls.lib().orc_features_in_area(_p(xy), _p(octave), len(xy), bounds[0], bounds[1], bounds[2], bounds[3], _p(qx), _p(qy), _p(qr),
                                              None if lo is None else _p(lo), None if hi is None else _p(hi), nq, _p(ptr), _p(cand), cap)
         return ptr, cand[:tot].copy()
+
+    @classmethod
+    def distinctive_descriptors(cls, desc, ptr):
+        """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:226-292) for len(ptr)-1 map points: (best_idx, best_median)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); ptr = np.ascontiguousarray(ptr, np.int32)
+        m = len(ptr) - 1
+        bi = np.zeros(m, np.int32); bm = np.zeros(m, np.int32)
+        cls.lib().orc_distinctive_descriptors(_p(desc), _p(ptr), m, _p(bi), _p(bm))
+        return bi, bm
 
     @classmethod
     def search_by_projection_frame(cls, Dq, Dc, ptr, cand, taken, angles_q=None, angles_c=None):

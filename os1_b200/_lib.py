@@ -44,6 +44,7 @@ SYMBOLS = [
     ("os1_undistort_keypoints", _i, [_vp, _i, _vp, _vp, _i, _i, _vp, _i, _i, _vp]),
     ("os1_image_bounds", _i, [_i, _i, _vp, _vp, _i, _i, _vp, _i]),
     ("os1_hamming_window", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    ("os1_distinctive_descriptors", _i, [_vp, _vp, _i, _vp, _vp, _i, _i, _vp]),
 ]
 
 _lib = None

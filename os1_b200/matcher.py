@@ -61,6 +61,19 @@ def hamming_window(A, B, ptr, cand, device=0):
     return bi, bd, sd
 
 
+def distinctive_descriptors(desc, ptr, device=0):
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:226-292) for len(ptr)-1 map points whose observation
+    descriptors are rows ptr[m]..ptr[m+1] of desc.  Returns (best_idx, best_median); best_idx is -1 for an empty point."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    ptr = np.ascontiguousarray(ptr, np.int32)
+    m = len(ptr) - 1
+    if m < 0:
+        raise ValueError("ptr must have at least one entry")
+    bi = np.zeros(max(m, 1), np.int32); bm = np.zeros(max(m, 1), np.int32)
+    _lib.check(_lib.load().os1_distinctive_descriptors(_ptr(desc) if len(desc) else None, _ptr(ptr), m, _ptr(bi), _ptr(bm), 0, device, None))
+    return bi[:m], bm[:m]
+
+
 def _csr(ptr, cand):
     return np.ascontiguousarray(ptr, np.int32), np.ascontiguousarray(cand, np.int32)
 
