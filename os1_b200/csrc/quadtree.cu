@@ -59,10 +59,42 @@ __device__ __forceinline__ int block_scan_excl(int v, int* warpSums, int& total)
     return warpSums[w] + inc - v;
 }
 
-// in-place bitonic sort of n64 (power of two) keys, descending when desc != 0
+// bitonic sort of n (a power of two) 64-bit keys in a[0..n), descending when desc != 0; `a` has room for 2n keys.
+// Up to one key per thread the keys stay in registers: partners less than 32 apart are exchanged by shuffles, the others
+// through shared memory, alternating between the two halves of `a` so that such a step costs one barrier — 10 barriers
+// instead of 45 for 512 keys, which is most of what a latency-bound CTA spends in its sorts.
 template <int QT_THREADS>
 __device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
 {
+    const int tid = threadIdx.x;
+    if (n <= QT_THREADS) {
+        unsigned long long x = tid < n ? a[tid] : 0ull;
+        int cur = 0;                        // which half of `a` the next shared-memory exchange writes
+#pragma unroll 1
+        for (int k = 2; k <= n; k <<= 1) {
+#pragma unroll 1
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                unsigned long long y;
+                if (j >= 32) {
+                    unsigned long long* buf = a + cur * n;
+                    if (tid < n) buf[tid] = x;
+                    __syncthreads();
+                    y = tid < n ? buf[tid ^ j] : 0ull;
+                    cur ^= 1;               // the next exchange writes the other half: no second barrier needed
+                } else {
+                    y = __shfl_xor_sync(0xffffffffu, x, j);
+                }
+                const bool lower = (tid & j) == 0;
+                const bool up = ((tid & k) == 0) != desc;
+                const bool takeMin = lower == up;
+                x = takeMin ? (x < y ? x : y) : (x < y ? y : x);
+            }
+        }
+        __syncthreads();                    // every exchange buffer has been read
+        if (tid < n) a[tid] = x;
+        __syncthreads();
+        return;
+    }
 #pragma unroll 1
     for (int k = 2; k <= n; k <<= 1)
 #pragma unroll 1
@@ -92,8 +124,8 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
     const int D = OS1_PATH_BITS;
 
     // ---- shared memory carve-up ---------------------------------------------------------------------------
-    unsigned long long* sortBuf = (unsigned long long*)smraw;                 // sortCap
-    uint32_t* cellOffs = (uint32_t*)(sortBuf + P.sortCap);                     // maxCells + 1
+    unsigned long long* sortBuf = (unsigned long long*)smraw;                 // 2 * sortCap (the sort ping-pongs)
+    uint32_t* cellOffs = (uint32_t*)(sortBuf + 2 * P.sortCap);                 // maxCells + 1
     uint32_t* slotCnt = cellOffs + P.maxCells + 1;                             // 4 * maxNodes
     uint32_t* slotInfo = slotCnt + 4 * P.maxNodes;                             // 4 * maxNodes
     uint32_t* liveSize = slotInfo + 4 * P.maxNodes;                            // maxNodes  (x2 buffers)
@@ -410,7 +442,7 @@ cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes
     P.maxCells = maxCells;
     int sc = 1; while (sc < max(P.maxNodes, P.maxLeaves)) sc <<= 1;
     P.sortCap = sc;
-    size_t smem = (size_t)P.sortCap * 8 + (size_t)(P.maxCells + 1) * 4 + (size_t)P.maxNodes * 4 * (4 + 4 + 2 + 2 + 1 + 1 + 1 + 1 + 1) + 8 * 4 +
+    size_t smem = (size_t)P.sortCap * 16 + (size_t)(P.maxCells + 1) * 4 + (size_t)P.maxNodes * 4 * (4 + 4 + 2 + 2 + 1 + 1 + 1 + 1 + 1) + 8 * 4 +
                   (size_t)P.maxLeaves * 8 + 34 * 4;
     if (smem > 220 * 1024 || P.maxNodes > 16000) return cudaErrorNotSupported;
     dim3 grid(nframes, g.nlevels);
