@@ -270,8 +270,8 @@ int build_geometry(os1_orb* h, int rows, int cols)
     if (h->planBig) os1_pyramid_plan_destroy(h->planBig);
     h->planBig = nullptr;
     {
-        // coarsest-level tile: 32x16 keeps a single frame spread over enough CTAs; batches use 40x20 (less halo,
-        // fewer block-wide phases).  A tile whose level-0 footprint exceeds a TMA box (256) falls back to a smaller one.
+        // coarsest-level tile: 32x16 keeps a single frame spread over enough CTAs.  A tile whose level-0 footprint exceeds a
+        // TMA box (256) falls back to a smaller one.
         const int cand[][2] = { { 32, 16 }, { 24, 12 }, { 16, 8 }, { 8, 8 } };
         for (auto& c : cand) {
             h->plan = os1_pyramid_plan_create(g, c[0], c[1]);
@@ -279,10 +279,15 @@ int build_geometry(os1_orb* h, int rows, int cols)
             os1_pyramid_plan_destroy(h->plan); h->plan = nullptr;
         }
         if (!h->plan) return fail(h, OS1_E_UNSUPPORTED, "no pyramid tile fits a TMA box for this scale factor / level count");
-        int tw = 40, th = 20;
-        if (const char* e = getenv("OS1_PYR_TILE")) sscanf(e, "%dx%d", &tw, &th);
-        h->planBig = os1_pyramid_plan_create(g, tw, th);
-        if (!os1_pyramid_plan_ok(h->planBig)) { os1_pyramid_plan_destroy(h->planBig); h->planBig = nullptr; }
+        // batches: the largest tile whose level-0 footprint still fits a TMA box (52x26 at scale 1.2 / 8 levels: 0.62 ms per
+        // 256 x 720p against 0.68 for 40x20 — less halo, fewer block-wide phases per pixel)
+        int big[][2] = { { 52, 26 }, { 40, 20 }, { 32, 16 }, { 24, 12 } };
+        if (const char* e = getenv("OS1_PYR_TILE")) sscanf(e, "%dx%d", &big[0][0], &big[0][1]);
+        for (auto& c : big) {
+            h->planBig = os1_pyramid_plan_create(g, c[0], c[1]);
+            if (os1_pyramid_plan_ok(h->planBig)) break;
+            os1_pyramid_plan_destroy(h->planBig); h->planBig = nullptr;
+        }
     }
     h->haveGeom = true;
     h->batchCap = 0;

@@ -347,14 +347,17 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
     P->boxW = (mw[0] + 15) & ~15;
     P->boxH = mh[0];
     p.boxBytes = P->boxW * P->boxH;
-    size_t off = 0;
+    // two shared-memory buffers, used alternately: level l+1 is written over level l-1, which nobody reads any more
+    // (the block-wide barrier after level l separates the two) — the tile chain costs size(L0) + size(L1), not the sum of
+    // all levels, and more CTAs fit an SM
+    size_t bufSize[2] = { 0, 0 };
     for (int l = 0; l < g.nlevels; l++) {
-        p.smemOff[l] = (int)off;
         p.smemPitch[l] = (l == 0) ? P->boxW : ((mw[l] + 3 + 3) & ~3);     // + up to 3 bytes: column 0 sits on a 4-px boundary
-        off += (size_t)p.smemPitch[l] * mh[l];
-        off = (off + 127) & ~(size_t)127;
+        bufSize[l & 1] = std::max(bufSize[l & 1], ((size_t)p.smemPitch[l] * mh[l] + 127) & ~(size_t)127);
         p.lvOff[l] = g.lv[l].off; p.lvPitch[l] = g.lv[l].pitch;
     }
+    for (int l = 0; l < g.nlevels; l++) p.smemOff[l] = (l & 1) ? (int)bufSize[0] : 0;
+    size_t off = bufSize[0] + bufSize[1];
     p.slabBytes = g.slabBytes;
     p.barOff = (int)off;
     P->smemBytes = off + 16 + 128;
