@@ -29,6 +29,9 @@
 #include "os1_internal.cuh"
 
 #define FAST_THREADS 256
+#ifndef FAST_MIN_CTAS
+#define FAST_MIN_CTAS 4
+#endif
 
 namespace {
 
@@ -127,7 +130,7 @@ __device__ __forceinline__ void arc_extremes(const unsigned (&W)[7][3], unsigned
 __device__ __forceinline__ unsigned usubsat2(unsigned a, unsigned b) { return __vmaxu2(a, b) - b; }     // max(a-b, 0)
 
 template <int PW>
-__global__ void __launch_bounds__(FAST_THREADS, 4) fast_kernel(const __grid_constant__ FastParams P)
+__global__ void __launch_bounds__(FAST_THREADS, FAST_MIN_CTAS) fast_kernel(const __grid_constant__ FastParams P)
 {
     extern __shared__ __align__(16) unsigned smw[];
     const Geometry& g = P.g;
@@ -452,7 +455,9 @@ cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cu
         maxCap = max(maxCap, g.lv[l].cellCap);
         if (g.lv[l].wCell > 64) return cudaErrorNotSupported;       // a cell's columns must fit the 64-bit row masks of phase 4
     }
-    const int need = ((maxW + 16) >> 2) + 4;           // + alignment slack (tile byte 0 sits on a 16-byte boundary) + whole 16-byte chunks
+    // widest tile: x0 - xorg <= 16 (tile byte 0 sits on a 16-byte boundary), one more word for the last group's right
+    // neighbour, rounded up to whole 16-byte chunks
+    const int need = (((((maxW + 16 + 3) >> 2) + 1) + 3) >> 2) << 2;
     const int PW = need <= 72 ? 72 : (need <= 88 ? 88 : 136);      // multiples of 4: tile rows are 16-byte aligned in shared memory
     if (need > 136) return cudaErrorNotSupported;
     P.pitchW = PW;
