@@ -13,8 +13,9 @@
 //
 // A CTA handles FAST_G horizontally adjacent cells of one cell row.  The work is integer-issue bound, so the
 // kernel is organised around instruction count, not bytes:
-//   phase 1  tile -> shared memory as aligned 32-bit words;
-//   phase 2  a thread scores FOUR adjacent pixels from 21 word loads: each ring value of a pixel pair sits in the high
+//   phase 1  tile -> shared memory with 16-byte asynchronous copies from a 16-byte aligned origin;
+//   phase 2  (after a cheap compass-point test that queues, per warp, the groups that can hold a corner at all)
+//            a thread scores FOUR adjacent pixels from 21 word loads: each ring value of a pixel pair sits in the high
 //            bytes of a u16x2 register (at most one byte-permute or shift, see ring_pair) and the min-of-9 / max-of-9
 //            arcs are min/max trees on the packed VIMNMX.U16x2 path (2 pixels/instr, 36 per polarity);
 //            the response is finished in packed form too (saturating differences as max(a,b)-b, no cross-lane
@@ -23,9 +24,9 @@
 //   phase 3  NMS as a column sweep: a thread owns one group of four columns and walks down a band of rows with the
 //            horizontal neighbour maxima of three rows in registers (4 word loads + ~25 ALU instructions per row,
 //            no divergence); cell boundaries are lane masks; survivors become bits of a per-row bitmap of the tile;
-//   phase 4  one warp per cell, one lane per row: cut the cell's columns out of the row bitmaps, vote "any survivor
-//            >= iniTh", take the exclusive prefix of the per-row counts and emit row by row, left to right — which is
-//            cv::FAST's output order, so nothing is ever sorted.
+//   phase 4  one warp per cell: lanes = rows cut the cell's columns out of the row bitmaps and write the survivors in
+//            row-major order (cv::FAST's output order) to a list; lanes = survivors vote "any survivor >= iniTh" and
+//            emit at their ballot rank, so nothing is ever sorted.
 #include "os1_internal.cuh"
 
 #define FAST_THREADS 256
@@ -147,7 +148,8 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MIN_CTAS) fast_kernel(const
     const int tw = x1 - x0, th = y1 - y0;
     constexpr int pw = PW;                 // compile-time pitch: every shared-memory access gets an immediate offset
     // shared memory: tile words; two score maps holding the even (px 0,2) and odd (px 1,3) pixels of every group
-    // of four as u16x2; six mask rows; per-cell survivor lists
+    // of four as u16x2; six mask rows; the survivor bitmap; the per-warp queues of phase 2 (the per-cell survivor lists of
+    // phase 4 reuse the image tile)
     unsigned* img = smw;
     unsigned* scE = img + pw * P.tileRows;
     unsigned* scO = scE + pw * P.tileRows;
