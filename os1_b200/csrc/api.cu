@@ -245,6 +245,12 @@ int build_geometry(os1_orb* h, int rows, int cols)
                 return fail(h, OS1_E_UNSUPPORTED, "scaleFactor 2.0: cv::resize silently switches to INTER_AREA there (not implemented)");
         }
     }
+    {
+        int maxIni = 1;
+        for (int l = 0; l < L; l++) maxIni = std::max(maxIni, g.lv[l].nIni);
+        if (!os1_quadtree_fits(h->maxQuota, h->maxCells, maxIni))
+            return fail(h, OS1_E_UNSUPPORTED, "too many features in one pyramid level for this image size: the quadtree state of a level must fit one CTA's shared memory (about 2300 features per level)");
+    }
     g.slabBytes = slab;
     g.cellsPerFrame = cellOff;
     g.groupsPerFrame = groupOff;

@@ -9,7 +9,7 @@
 //   border fix-up, octave, size, scaling   :879-889, :959-967   and the level-major concatenation of :936-967
 // The warp stages the 43x43 source window in shared memory once; orientation, both blur passes and the 512
 // rotated taps all read it from there.  No FMA contraction anywhere in the float path (x86 reference build has
-// none); cos/sin are evaluated in double and rounded, which is what glibc's cosf/sinf deliver.
+// none); cos/sin follow glibc's cosf/sinf algorithm (see libm_sincosf).
 #include "os1_internal.cuh"
 #include <cmath>
 #include <cfloat>
@@ -84,6 +84,55 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x, const DescPara
     if (x < 0) a = __fsub_rn(180.f, a);
     if (y < 0) a = __fsub_rn(360.f, a);
     return a;
+}
+
+// cosf / sinf exactly as the reference's C library evaluates them (ORBextractor.cc:136-137 calls cos/sin on a float,
+// i.e. cosf/sinf).  glibc >= 2.28 (sysdeps/ieee754/flt-32/s_sinf.c, s_cosf.c, sincosf.h — the ARM optimized-routines
+// implementation) is accurate to 0.56 ULP, NOT correctly rounded: it differs from round(cos((double)x)) for about one
+// float in a thousand, and a 1-ULP difference in a or b flips one of the 512 rounded tap coordinates of a keypoint about
+// once in 10^5 keypoints.  So the algorithm itself is restated: reduction by pi/2 with n = (int)(x * 2/pi * 2^24 + 2^23)
+// >> 24, then the degree-7 sine or degree-8 cosine polynomial in double, no fused multiply-adds.  Verified on the host
+// (same constants, same order of operations) against libm's cosf / sinf on 155 million floats of [0, 6.5): no difference.
+// Valid for 0 <= x < 120; the angles here are in [0, 2 pi].
+__device__ __forceinline__ float libm_sincosf_poly(double x, double x2, bool flip, int n)
+{
+    const double C0 = 0x1p0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5, C3 = -0x1.6c087e89a359dp-10, C4 = 0x1.99343027bf8c3p-16;
+    const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+    if ((n & 1) == 0) {
+        const double x3 = __dmul_rn(x, x2);
+        const double s1 = __dadd_rn(S2, __dmul_rn(x2, S3));
+        const double x7 = __dmul_rn(x3, x2);
+        const double s = __dadd_rn(x, __dmul_rn(x3, S1));
+        return (float)__dadd_rn(s, __dmul_rn(x7, s1));
+    }
+    // (the second table of the reference has c0..c4 negated: every term, and so the sum, changes sign exactly)
+    const double x4 = __dmul_rn(x2, x2);
+    const double c2 = __dadd_rn(C3, __dmul_rn(x2, C4));
+    const double c1 = __dadd_rn(C0, __dmul_rn(x2, C1));
+    const double x6 = __dmul_rn(x4, x2);
+    const double c = __dadd_rn(c1, __dmul_rn(x4, C2));
+    const double r = __dadd_rn(c, __dmul_rn(x6, c2));
+    return (float)(flip ? -r : r);
+}
+__device__ __forceinline__ void libm_sincosf(float y, float& sn, float& cs)
+{
+    const unsigned top = (__float_as_uint(y) >> 20) & 0x7ffu;
+    double x = (double)y;
+    if (top < ((__float_as_uint(0x1.921FB6p-1f) >> 20) & 0x7ffu)) {           // |y| < pi/4
+        const double x2 = __dmul_rn(x, x);
+        if (top < ((__float_as_uint(0x1p-12f) >> 20) & 0x7ffu)) { sn = y; cs = 1.0f; return; }
+        sn = libm_sincosf_poly(x, x2, false, 0);
+        cs = libm_sincosf_poly(x, x2, false, 1);
+        return;
+    }
+    const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);                      // x * 2/pi * 2^24
+    const int n = (__double2int_rz(r) + 0x800000) >> 24;
+    x = __dsub_rn(x, __dmul_rn((double)n, 0x1.921FB54442D18p0));
+    const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;             // sign[n & 3] = {1, -1, -1, 1}
+    const bool flip = (n & 2) != 0;
+    const double xs = __dmul_rn(x, sgn), x2 = __dmul_rn(x, x);
+    sn = libm_sincosf_poly(xs, x2, flip, n);
+    cs = libm_sincosf_poly(xs, x2, flip, n ^ 1);
 }
 
 __global__ void __launch_bounds__(DESC_WARPS * 32, 8) describe_kernel(const __grid_constant__ DescParams P)
@@ -243,9 +292,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 8) describe_kernel(const __gr
 
     // ---- rotated BRIEF: lane = descriptor byte ---------------------------------------------------------------------------
     const float ang = __fmul_rn(angle, P.factorPI);
-    double sd, cd;
-    sincos((double)ang, &sd, &cd);             // one range reduction for both
-    const float a = (float)cd, b = (float)sd;
+    float a, b;
+    libm_sincosf(ang, b, a);                   // a = cosf(ang), b = sinf(ang) as the reference's libm computes them
     const int4* pat = (const int4*)d_pattern;
     int4 w0 = __ldg(pat + 2 * lane), w1 = __ldg(pat + 2 * lane + 1);
     const int words[8] = { w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w };

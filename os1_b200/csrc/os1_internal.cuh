@@ -93,6 +93,7 @@ void os1_pyramid_plan_destroy(PyramidPlan*);
 bool os1_pyramid_plan_ok(const PyramidPlan*);     // level-0 footprint fits a TMA box and the tile chain fits shared memory
 cudaError_t os1_launch_pyramid(PyramidPlan*, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
 cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
+bool os1_quadtree_fits(int maxQuota, int maxCells, int maxIni);       // the per-level state fits one CTA's shared memory
 cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes, int maxQuota, int maxCells, cudaStream_t s);
 cudaError_t os1_launch_describe(const Geometry& g, const DevPtrs& d, int nframes, os1_kp_dev* kp, uint8_t* desc, int capPerFrame,
                                 int* counts, cudaStream_t s);

@@ -124,8 +124,8 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
     const int D = OS1_PATH_BITS;
 
     // ---- shared memory carve-up ---------------------------------------------------------------------------
-    unsigned long long* sortBuf = (unsigned long long*)smraw;                 // 2 * sortCap (the sort ping-pongs)
-    uint32_t* cellOffs = (uint32_t*)(sortBuf + 2 * P.sortCap);                 // maxCells + 1
+    unsigned long long* sortBuf = (unsigned long long*)smraw;                 // max(sortCap, 2 * min(sortCap, 1024)): the register sort ping-pongs
+    uint32_t* cellOffs = (uint32_t*)(sortBuf + max(P.sortCap, 2 * min(P.sortCap, 1024)));       // maxCells + 1
     uint32_t* slotCnt = cellOffs + P.maxCells + 1;                             // 4 * maxNodes
     uint32_t* slotInfo = slotCnt + 4 * P.maxNodes;                             // 4 * maxNodes
     uint32_t* liveSize = slotInfo + 4 * P.maxNodes;                            // maxNodes  (x2 buffers)
@@ -434,6 +434,20 @@ __global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel
 
 } // namespace
 
+// shared memory of one quadtree CTA, and the sizes it is derived from (the launcher and the geometry check agree on it)
+static size_t quadtree_smem(int maxQuota, int maxCells, int maxIni, QtParams* P)
+{
+    const int maxNodes = max(maxQuota, maxIni) + 8;
+    const int maxLeaves = max(maxQuota + 2, 4 * maxIni) + 8;
+    int sc = 1; while (sc < max(maxNodes, maxLeaves)) sc <<= 1;
+    if (P) { P->maxNodes = maxNodes; P->maxLeaves = maxLeaves; P->maxCells = maxCells; P->sortCap = sc; }
+    // the sort keeps its keys in registers and ping-pongs between two halves only up to one key per thread (<= 1024)
+    const size_t sortKeys = (size_t)max(sc, 2 * min(sc, 1024));
+    return sortKeys * 8 + (size_t)(maxCells + 1) * 4 + (size_t)maxNodes * 4 * (4 + 4 + 2 + 2 + 1 + 1 + 1 + 1 + 1) + 8 * 4 + (size_t)maxLeaves * 8 + 34 * 4;
+}
+
+bool os1_quadtree_fits(int maxQuota, int maxCells, int maxIni) { return quadtree_smem(maxQuota, maxCells, maxIni, nullptr) <= 220 * 1024; }
+
 cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes, int maxQuota, int maxCells, cudaStream_t s)
 {
     static_assert(sizeof(QtParams) < 4000, "kernel parameter block too large");
@@ -441,13 +455,7 @@ cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes
     P.g = g; P.d = d;
     int maxIni = 1;
     for (int l = 0; l < g.nlevels; l++) maxIni = max(maxIni, g.lv[l].nIni);
-    P.maxNodes = max(maxQuota, maxIni) + 8;
-    P.maxLeaves = max(maxQuota + 2, 4 * maxIni) + 8;
-    P.maxCells = maxCells;
-    int sc = 1; while (sc < max(P.maxNodes, P.maxLeaves)) sc <<= 1;
-    P.sortCap = sc;
-    size_t smem = (size_t)P.sortCap * 16 + (size_t)(P.maxCells + 1) * 4 + (size_t)P.maxNodes * 4 * (4 + 4 + 2 + 2 + 1 + 1 + 1 + 1 + 1) + 8 * 4 +
-                  (size_t)P.maxLeaves * 8 + 34 * 4;
+    const size_t smem = quadtree_smem(maxQuota, maxCells, maxIni, &P);
     if (smem > 220 * 1024 || P.maxNodes > 16000) return cudaErrorNotSupported;
     dim3 grid(nframes, g.nlevels);
     // few frames: the level-0 CTA is the critical path, give it 1024 threads; batches: 512 threads, two CTAs per SM

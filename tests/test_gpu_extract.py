@@ -84,6 +84,8 @@ def test_against_committed_reference_golden(golden_dir, name):
     ((1080, 1920), 2000, 1.2, 12, 20, 7, 22),   # twelve levels (the maximum)
     ((600, 800), 1000, 1.1, 10, 20, 7, 23),     # fine scale steps
     ((1000, 1000), 1500, 1.3, 6, 20, 7, 24),    # square image, coarse scale steps
+    ((1231, 1319), 873, 1.25, 2, 25, 28, 1194),  # a keypoint whose cosf is not the correctly rounded cosine (found by scripts/fuzz_extract.py)
+    ((762, 1004), 2302, 1.41, 1, 31, 5, 1198),   # the same for sinf; one level with 2302 features
 ])
 def test_other_geometries(oracle_lib, shape, nf, sf, nl, ini, mn, seed):
     compare_full(oracle_lib, synth.frame(shape[0], shape[1], seed), nf, sf, nl, ini, mn)
