@@ -192,6 +192,24 @@ def extras(torch, os1_b200, dev):
     for _ in range(200):
         t = time.perf_counter(); e(img); ts.append(time.perf_counter() - t)
     out["latency_ms_640x480_1000feat_host_to_host"] = float(np.median(ts) * 1e3)
+    # the other two resolutions of BASELINE.json's metric line (configs[0] and configs[2]), frames resident in HBM
+    for name, (hh, ww, nfeat, nb) in (("640x480_1000feat", (480, 640, 1000, 512)), ("1920x1080_2000feat", (1080, 1920, 2000, 128))):
+        ex = os1_b200.ORBextractor(nfeat, 1.2, 8, 20, 7, device=dev.index)
+        vid = torch.from_numpy(synth.video(nb, hh, ww, seed=31)).to(dev)
+        capx = ex.max_keypoints(); ex.reserve(hh, ww, nb)
+        st = torch.cuda.Stream(dev); ex.set_stream(st.cuda_stream)        # (a real stream: 0 would mean "the handle's own")
+        kpx = torch.empty((nb, capx, 28), dtype=torch.uint8, device=dev); dex = torch.empty((nb, capx, 32), dtype=torch.uint8, device=dev)
+        cnx = torch.zeros(nb, dtype=torch.int32, device=dev)
+        run = lambda: ex.extract_batch_raw(vid.data_ptr(), nb, hh, ww, ww, hh * ww, True, kpx.data_ptr(), dex.data_ptr(), capx, cnx.data_ptr(), True)
+        for _ in range(3):
+            run()
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(dev); t0.record(st)
+        for _ in range(10):
+            run()
+        t1.record(st); torch.cuda.synchronize(dev); ex.synchronize()
+        out["frames_per_s_%s_device_resident" % name] = nb * 10 / (t0.elapsed_time(t1) * 1e-3)
+        del ex, vid, kpx, dex, cnx
     # config 4: 2000 x 2000 descriptors of two frames extracted with the 2000-feature extractor, all on device
     fr = synth.video(2, 720, 1280, seed=9)
     e2 = os1_b200.ORBextractor(2000, 1.2, 8, 20, 7, device=dev.index)
