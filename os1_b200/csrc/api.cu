@@ -321,8 +321,10 @@ int ensure(os1_orb* h, int rows, int cols, int nframes)
         CK(h->candCount.ensure(B * g.nlevels * 4), "cudaMalloc(candidate counts)");
         CK(h->lvKp.ensure(B * g.kpCapPerFrame * 4), "cudaMalloc(level keypoints)");
         CK(h->lvCount.ensure(B * g.nlevels * 4), "cudaMalloc(level counts)");
-        CK(h->status.ensure(256), "cudaMalloc(status)");
-        CK(cudaMemset(h->status.p, 0, 256), "cudaMemset(status)");
+        // status word (offset 0), then the single-frame outputs — count (offset 4), keypoints (offset 64), descriptors — so
+        // that the latency path fetches everything with ONE device-to-host copy
+        CK(h->status.ensure(64 + (size_t)g.kpCapPerFrame * (sizeof(os1_kp_dev) + 32)), "cudaMalloc(status + single-frame outputs)");
+        CK(cudaMemset(h->status.p, 0, 64), "cudaMemset(status)");
         CK(h->outKp.ensure(B * g.kpCapPerFrame * sizeof(os1_kp_dev)), "cudaMalloc(keypoints)");
         CK(h->outDesc.ensure(B * g.kpCapPerFrame * 32), "cudaMalloc(descriptors)");
         CK(h->outCount.ensure(B * 4), "cudaMalloc(counts)");
@@ -587,18 +589,18 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     // ---- one frame from the host: the latency path --------------------------------------------------------------------------
     if (nframes == 1 && !out_on_device) {
         if (!direct) CK(stage_in(0, 1, h->stream), "upload frame");
-        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, 1, dKp, dDesc, dCap, dCnt);
+        uint8_t* sb = (uint8_t*)h->status.p;                       // [status | count | pad to 64 | keypoints | descriptors]
+        const size_t slabBytes = 64 + (size_t)cap * (sizeof(os1_kp_dev) + 32);
+        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, 1, (os1_kp_dev*)(sb + 64), sb + 64 + (size_t)cap * sizeof(os1_kp_dev), cap, (int*)(sb + 4));
         if (rc) return rc;
         uint8_t* hb = (uint8_t*)h->hostOut;
-        os1_kp_dev* hk = (os1_kp_dev*)hb;
-        uint8_t* hd = hb + (size_t)cap * sizeof(os1_kp_dev);
-        int* hc = (int*)(hd + (size_t)cap * 32);
-        // one round trip: the count, the status word and the (small, fixed-size) output slabs travel together
-        CK(cudaMemcpyAsync(hc, dCnt, 4, cudaMemcpyDeviceToHost, h->stream), "download count");
-        CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
-        CK(cudaMemcpyAsync(hk, dKp, (size_t)cap * sizeof(os1_kp_dev), cudaMemcpyDeviceToHost, h->stream), "download keypoints");
-        CK(cudaMemcpyAsync(hd, dDesc, (size_t)cap * 32, cudaMemcpyDeviceToHost, h->stream), "download descriptors");
+        os1_kp_dev* hk = (os1_kp_dev*)(hb + 64);
+        uint8_t* hd = hb + 64 + (size_t)cap * sizeof(os1_kp_dev);
+        int* hc = (int*)(hb + 4);
+        // one round trip, one copy: the status word, the count and the (small, fixed-size) output slabs travel together
+        CK(cudaMemcpyAsync(hb, sb, slabBytes, cudaMemcpyDeviceToHost, h->stream), "download outputs");
         CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+        h->hostStatus[0] = *(int*)hb;
         rc = check_status(h, h->hostStatus[0]);
         if (rc) return rc;
         const int n = std::min(hc[0], cap);
