@@ -54,6 +54,11 @@ struct os1_orb {
     Geometry geom;
     int maxCells = 0;
     int batchCap = 0;
+    // latency path: the four launches and the result copy of a single host frame as one CUDA graph (built on the third
+    // call of a geometry, dropped whenever a buffer it points to is reallocated)
+    cudaGraphExec_t latExec = nullptr;
+    int latCalls = 0;
+    bool latDisabled = false;
     PyramidPlan* plan = nullptr;        // small tiles (single frames)
     PyramidPlan* planBig = nullptr;     // larger tiles (batches)
     DevBuf rtab, ptab, gtab, slab, cellCnt, stage, cand, code, node, candCount, lvKp, lvCount, status, outKp, outDesc, outCount;
@@ -305,12 +310,16 @@ int ensure(os1_orb* h, int rows, int cols, int nframes)
     CK(cudaSetDevice(h->device), "cudaSetDevice");
     if (!h->haveGeom || h->geom.rows != rows || h->geom.cols != cols) {
         if (h->haveGeom) CK(cudaStreamSynchronize(h->stream), "sync before re-planning");
+        if (h->latExec) { cudaGraphExecDestroy(h->latExec); h->latExec = nullptr; }
+        h->latCalls = 0;
         int rc = build_geometry(h, rows, cols);
         if (rc) return rc;
     }
     if (nframes > h->batchCap) {
         const Geometry& g = h->geom;
         CK(cudaStreamSynchronize(h->stream), "sync before growing buffers");
+        if (h->latExec) { cudaGraphExecDestroy(h->latExec); h->latExec = nullptr; }
+        h->latCalls = 0;
         const size_t B = (size_t)nframes;
         CK(h->slab.ensure(B * g.slabBytes + 256), "cudaMalloc(pyramid slab)");
         CK(h->cellCnt.ensure(B * g.cellsPerFrame * 4), "cudaMalloc(cell counts)");
@@ -431,9 +440,10 @@ int os1_orb_destroy(os1_orb* h)
     if (!h) return OS1_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    if (h->latExec) cudaGraphExecDestroy(h->latExec);
     if (h->plan) os1_pyramid_plan_destroy(h->plan);
     if (h->planBig) os1_pyramid_plan_destroy(h->planBig);
-    DevBuf* bufs[] = { &h->rtab, &h->ptab, &h->slab, &h->cellCnt, &h->stage, &h->cand, &h->code, &h->node, &h->candCount,
+    DevBuf* bufs[] = { &h->rtab, &h->ptab, &h->gtab, &h->slab, &h->cellCnt, &h->stage, &h->cand, &h->code, &h->node, &h->candCount,
                        &h->lvKp, &h->lvCount, &h->status, &h->outKp, &h->outDesc, &h->outCount };
     for (DevBuf* b : bufs) b->release();
     if (h->hostOut) cudaFreeHost(h->hostOut);
@@ -591,14 +601,39 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
         if (!direct) CK(stage_in(0, 1, h->stream), "upload frame");
         uint8_t* sb = (uint8_t*)h->status.p;                       // [status | count | pad to 64 | keypoints | descriptors]
         const size_t slabBytes = 64 + (size_t)cap * (sizeof(os1_kp_dev) + 32);
-        rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, 1, (os1_kp_dev*)(sb + 64), sb + 64 + (size_t)cap * sizeof(os1_kp_dev), cap, (int*)(sb + 4));
-        if (rc) return rc;
         uint8_t* hb = (uint8_t*)h->hostOut;
         os1_kp_dev* hk = (os1_kp_dev*)(hb + 64);
         uint8_t* hd = hb + 64 + (size_t)cap * sizeof(os1_kp_dev);
         int* hc = (int*)(hb + 4);
-        // one round trip, one copy: the status word, the count and the (small, fixed-size) output slabs travel together
-        CK(cudaMemcpyAsync(hb, sb, slabBytes, cudaMemcpyDeviceToHost, h->stream), "download outputs");
+        static const bool useGraph = !(getenv("OS1_GRAPH") && atoi(getenv("OS1_GRAPH")) == 0);
+        const bool graphOk = useGraph && !h->latDisabled && !frames_on_device && !h->timing;
+        bool done = false;
+        if (graphOk && h->latExec) {
+            CK(cudaGraphLaunch(h->latExec, h->stream), "cudaGraphLaunch");
+            done = true;
+        } else if (graphOk && ++h->latCalls >= 3) {
+            // (the first calls run plainly: lazily initialised tables and function attributes must exist before a capture)
+            cudaGraph_t gph = nullptr;
+            if (cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+                const int rcc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, 1, (os1_kp_dev*)(sb + 64), sb + 64 + (size_t)cap * sizeof(os1_kp_dev), cap, (int*)(sb + 4));
+                cudaError_t ce = rcc ? cudaErrorUnknown : cudaMemcpyAsync(hb, sb, slabBytes, cudaMemcpyDeviceToHost, h->stream);
+                cudaError_t ee = cudaStreamEndCapture(h->stream, &gph);
+                if (ce == cudaSuccess && ee == cudaSuccess && gph && cudaGraphInstantiate(&h->latExec, gph, 0) == cudaSuccess) {
+                    CK(cudaGraphLaunch(h->latExec, h->stream), "cudaGraphLaunch");
+                    done = true;
+                } else {
+                    cudaGetLastError();
+                    h->latExec = nullptr; h->latDisabled = true;          // this driver / stream cannot capture the sequence: plain launches from now on
+                }
+                if (gph) cudaGraphDestroy(gph);
+            } else { cudaGetLastError(); h->latDisabled = true; }
+        }
+        if (!done) {
+            rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, 1, (os1_kp_dev*)(sb + 64), sb + 64 + (size_t)cap * sizeof(os1_kp_dev), cap, (int*)(sb + 4));
+            if (rc) return rc;
+            // one round trip, one copy: the status word, the count and the (small, fixed-size) output slabs travel together
+            CK(cudaMemcpyAsync(hb, sb, slabBytes, cudaMemcpyDeviceToHost, h->stream), "download outputs");
+        }
         CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
         h->hostStatus[0] = *(int*)hb;
         rc = check_status(h, h->hostStatus[0]);

@@ -91,3 +91,29 @@ def test_reserve_and_foreign_stream(oracle_lib):
     for f in range(4):
         ko, do = o.extract(fr[f])
         assert int(cnt[f]) == len(ko) and np.array_equal(desc[f, :len(ko)].cpu().numpy(), do)
+
+
+def test_latency_graph_replays_follow_the_input(oracle_lib):
+    """From the third call of a geometry on, a single host frame runs as one CUDA graph: every replay must see the new
+    pixels, and the graph must be rebuilt when a batch call reallocates the buffers it points to."""
+    import os1_b200
+    from os1_b200 import synth
+    e = os1_b200.ORBextractor(800, 1.2, 8, 20, 7)
+    o = oracle_lib.Oracle(800, 1.2, 8, 20, 7)
+    frames = synth.video(8, 360, 480, seed=77, max_shift=10)
+
+    def same(i):
+        kg, dg = e(frames[i])
+        r = o.extract(frames[i])
+        return len(kg) == len(r[0]) and np.array_equal(dg, r[1]) and np.array_equal(kg["angle"], r[0][:, 3])
+
+    assert all(same(i) for i in range(5))                      # plain, plain, capture, replay, replay
+    kb, db, cb = e.extract_batch(frames)                       # grows the per-frame buffers: the graph is dropped
+    for i in range(8):
+        r = o.extract(frames[i])
+        assert cb[i] == len(r[0]) and np.array_equal(db[i, :cb[i]], r[1])
+    assert all(same(i) for i in (7, 6, 5, 4, 3))               # and rebuilt
+    e.set_timing(True)                                         # timed calls bypass the graph
+    assert same(0) and len(e.stage_times_ms()) == 4
+    e.set_timing(False)
+    assert same(1)
