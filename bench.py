@@ -312,7 +312,8 @@ def run_ours(args, rank, world, local_rank):
     cap = ext.max_keypoints()
     ext.reserve(ROWS, COLS, B)
     stream = torch.cuda.current_stream(dev)
-    ext.set_stream(stream.cuda_stream)
+    xstream = torch.cuda.Stream(dev)                 # the extractor's stream: kernels and timing events share it
+    ext.set_stream(xstream.cuda_stream)
     kp_d = torch.empty((B, cap, 28), dtype=torch.uint8, device=dev)
     desc_d = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
     cnt_d = torch.zeros(B, dtype=torch.int32, device=dev)
@@ -348,11 +349,11 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     stage_ms = np.zeros(4)
-    e0.record(stream)
+    e0.record(xstream)
     for _ in range(args.steps):
         step_device()
         stage_ms += ext.stage_times_ms()        # waits for this step's last event: steps are serialised anyway
-    e1.record(stream)
+    e1.record(xstream)
     barrier()
     ms = e0.elapsed_time(e1)
     if not sampler.rows:

@@ -224,16 +224,13 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MIN_CTAS) fast_kernel(const
 #pragma unroll 1
     for (int i = tid; 4 * i < th * bw; i += FAST_THREADS) ((uint4*)bm)[i] = make_uint4(0, 0, 0, 0);
     const int g0 = tc0 >> 2, g1 = (tc1 + 3) >> 2;
-    // the NMS reads one word / one row beyond the scored area: only that frame has to be zero
+    // both score maps start as zeros (16-byte stores): the groups the compass test rejects are never touched again, and the
+    // NMS may read one word / one row beyond the scored area
+    {
+        uint4* z = (uint4*)scE;                       // scE and scO are adjacent; pw is a multiple of 4
+        const int nz = (pw * P.tileRows + pw * th) >> 2;
 #pragma unroll 1
-    for (int w = g0 - 1 + tid; w <= g1; w += FAST_THREADS) {
-        scE[(tr0 - 1) * pw + w] = 0; scO[(tr0 - 1) * pw + w] = 0;
-        scE[tr1 * pw + w] = 0; scO[tr1 * pw + w] = 0;
-    }
-#pragma unroll 1
-    for (int r = tr0 + tid; r < tr1; r += FAST_THREADS) {
-        scE[r * pw + g0 - 1] = 0; scO[r * pw + g0 - 1] = 0;
-        scE[r * pw + g1] = 0; scO[r * pw + g1] = 0;
+        for (int i = tid; i < nz; i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
     asm volatile("cp.async.wait_all;" ::: "memory");
     __syncthreads();
@@ -280,7 +277,6 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MIN_CTAS) fast_kernel(const
                     u[odd] = __vmaxu2(usubsat2(lo, c), usubsat2(c | 0x00FF00FFu, hi));
                 }
                 pass = (usubsat2(u[0], T1) | usubsat2(u[1], T1)) != 0;
-                if (!pass) { scE[r * pw + gq] = 0; scO[r * pw + gq] = 0; }
             }
             const unsigned bal = __ballot_sync(0xffffffffu, pass);
             if (pass) queue[qn + __popc(bal & ltmask)] = (unsigned short)idx;
