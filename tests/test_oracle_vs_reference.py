@@ -83,3 +83,12 @@ def test_glibc_allocator_divergence_is_small(oracle_lib, golden_dir):
     final cut: a handful of keypoints per frame, reported not hidden."""
     g = np.load(os.path.join(golden_dir, "extract_vga.npz"))
     assert int(g["glibc_only"]) <= 30 and int(g["canon_only"]) <= 30
+
+
+def test_fuzz_oracle_against_reference():
+    """Random geometries / parameters: the restatement against the unmodified reference (scripts/fuzz_oracle_vs_reference.py)."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "fuzz_oracle_vs_reference.py"), "24", "500"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "mismatches 0" in r.stdout or "nothing to compare" in r.stdout
