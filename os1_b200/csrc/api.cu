@@ -425,7 +425,10 @@ int os1_orb_create(os1_orb** out, int nfeatures, float scaleFactor, int nlevels,
     h->scaleFactor = scaleFactor;
     h->device = device;
     build_tables(h);
-    if (h->maxQuota > 4000) { delete h; return fail(nullptr, OS1_E_UNSUPPORTED, "os1_orb_create: more than 4000 features in one level"); }
+    if (!os1_quadtree_fits(h->maxQuota, 0, 1)) {      // (the image size adds its cell table to this: checked again per geometry)
+        delete h;
+        return fail(nullptr, OS1_E_UNSUPPORTED, "os1_orb_create: too many features in one pyramid level (the quadtree state of a level must fit one CTA's shared memory: about 2300)");
+    }
     if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) {
         delete h;
         return cuda_fail(nullptr, e, "os1_orb_create");

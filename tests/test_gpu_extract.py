@@ -80,7 +80,7 @@ def test_against_committed_reference_golden(golden_dir, name):
     ((85, 85), 60, 1.2, 1, 20, 7, 11),          # one FAST cell of 59 x 59: the widest and tallest a cell can be
     ((80, 100), 100, 1.2, 2, 20, 7, 12),        # cells wider than 32 columns, one cell row taller than 32
     ((220, 800), 400, 1.2, 3, 20, 7, 13),       # four quadtree roots (the widest aspect supported)
-    ((2160, 3840), 4000, 1.2, 8, 20, 7, 21),    # 4K, as many features per level as the limits allow
+    ((2160, 3840), 4000, 1.2, 8, 20, 7, 21),    # 4K, 4000 features
     ((1080, 1920), 2000, 1.2, 12, 20, 7, 22),   # twelve levels (the maximum)
     ((600, 800), 1000, 1.1, 10, 20, 7, 23),     # fine scale steps
     ((1000, 1000), 1500, 1.3, 6, 20, 7, 24),    # square image, coarse scale steps

@@ -117,3 +117,15 @@ def test_latency_graph_replays_follow_the_input(oracle_lib):
     assert same(0) and len(e.stage_times_ms()) == 4
     e.set_timing(False)
     assert same(1)
+
+
+def test_feature_limit_is_reported_as_unsupported():
+    """A level's quadtree state must fit one CTA's shared memory: too many features in one level is OS1_E_UNSUPPORTED at
+    create time (or at the first frame, when the image's cell table tips it over), never a CUDA launch failure."""
+    import os1_b200
+    with pytest.raises(os1_b200.Os1Error) as ei:
+        os1_b200.ORBextractor(6000, 1.2, 1, 20, 7)
+    assert ei.value.code == -4
+    e = os1_b200.ORBextractor(2200, 1.2, 1, 20, 7)            # fits
+    kp, d = e(synth.frame(480, 640, 3))
+    assert len(kp) > 1500
