@@ -75,7 +75,10 @@ int os1_orb_extract(os1_orb* h, const uint8_t* image, int rows, int cols, size_t
  * frames_on_device / out_on_device say whether those pointers are device memory of the handle's GPU.
  * Outputs are slabs of cap_per_frame records per frame: kp[f*cap + i], desc[(f*cap + i)*32], counts[f].
  * With every buffer on the device the call only enqueues work on the handle's stream (see os1_orb_synchronize);
- * device-side failures are then reported by os1_orb_synchronize. */
+ * device-side failures are then reported by os1_orb_synchronize.
+ * Host buffers are copied in chunks that overlap with the kernels: give it page-locked memory (cudaHostAlloc /
+ * cudaHostRegister) — with pageable memory the copies are staged by the driver and nothing overlaps.  Slots beyond
+ * counts[f] of a frame are not meaningful. */
 int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int rows, int cols, size_t step, size_t frame_stride,
                           int frames_on_device, os1_keypoint* kp, uint8_t* desc, int cap_per_frame, int* counts, int out_on_device);
 int os1_orb_synchronize(os1_orb* h);
