@@ -42,11 +42,12 @@ struct DescParams {
 };
 
 struct WarpSmem {
-    uint4 raw4[WIN * RAW_PW / 4];       // source window as fetched: window column c sits at byte c + shift (< 16);
-                                        // after the horizontal pass the same words hold the blurred 37x37 window (bytes)
-    uint4 hp[HB_PAIRS * HB_Q];          // horizontal pass, per PAIR of rows (2e, 2e+1) and group of four columns:
-                                        // four u16x2 words {H[2e][j] | H[2e+1][j] << 16}, j = 4q .. 4q+3
+    uint4 raw4[HB_PAIRS * HB_Q];        // source window as fetched (43 rows of 80 bytes: window column c sits at byte c + shift,
+                                        // shift < 16), overwritten IN PLACE by the horizontal pass: a pair of rows (2e, 2e+1) is 160
+                                        // bytes, and so are its ten groups of four u16x2 words {H[2e][j] | H[2e+1][j] << 16}
+    unsigned bl[HB_W * (BL_PITCH / 4)]; // the blurred 37x37 window (bytes, 40-byte rows)
 };
+static_assert(HB_PAIRS * HB_Q * 16 >= WIN * RAW_PW * 4 && 2 * RAW_PW * 4 == HB_Q * 16, "a row pair and its horizontal-pass output must overlay exactly");
 
 // Intensity-centroid coefficients, one row of the 31x31 patch per lane: for |v| = 0..15 and the nine aligned words that
 // hold patch columns 4..39 of the window, the signed column offsets u (0 outside the circle) and the 0/1 membership
@@ -135,7 +136,7 @@ __device__ __forceinline__ void libm_sincosf(float y, float& sn, float& cs)
     cs = libm_sincosf_poly(xs, x2, flip, n ^ 1);
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32, 8) describe_kernel(const __grid_constant__ DescParams P)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __grid_constant__ DescParams P)
 {
     __shared__ WarpSmem sm[DESC_WARPS];
     __shared__ IcTab ic;
@@ -236,26 +237,32 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 8) describe_kernel(const __gr
     // two rows (<= 65280 each) are packed as u16x2 so that the vertical pass can use dp2a on them.
     {
         const unsigned K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K2 = 48u | (34u << 8) | (18u << 16);
-        for (int it = lane; it < HB_PAIRS * HB_Q; it += 32) {
-            const int e = (it * 6554) >> 16;            // it / 10
-            const int q = it - e * HB_Q;
+        // (three pairs per trip, lanes 30 and 31 idle: every lane of a pair has read its rows before any of them writes)
+        const int sub = lane / HB_Q, q = lane - sub * HB_Q;
+        for (int e0 = 0; e0 < HB_PAIRS; e0 += 3) {
+            const int e = e0 + sub;
+            const bool on = sub < 3 && e < HB_PAIRS;
             unsigned h[2][4];
+            if (on) {
 #pragma unroll
-            for (int rr = 0; rr < 2; rr++) {
-                const int r = min(2 * e + rr, WIN - 1);
-                const unsigned* w = raw + r * RAW_PW + q;
-                const unsigned W0 = w[0], W1 = w[1], W2 = w[2], W3 = w[3];
-                const unsigned A0 = __funnelshift_r(W0, W1, s8), A1 = __funnelshift_r(W1, W2, s8), A2 = __funnelshift_r(W2, W3, s8);
-                h[rr][0] = __dp4a(A0, K1, __dp4a(A1, K2, 0u));
-                h[rr][1] = __dp4a(__funnelshift_r(A0, A1, 8), K1, __dp4a(__funnelshift_r(A1, A2, 8), K2, 0u));
-                h[rr][2] = __dp4a(__funnelshift_r(A0, A1, 16), K1, __dp4a(__funnelshift_r(A1, A2, 16), K2, 0u));
-                h[rr][3] = __dp4a(__funnelshift_r(A0, A1, 24), K1, __dp4a(__funnelshift_r(A1, A2, 24), K2, 0u));
+                for (int rr = 0; rr < 2; rr++) {
+                    const int r = min(2 * e + rr, WIN - 1);
+                    const unsigned* w = raw + r * RAW_PW + q;
+                    const unsigned W0 = w[0], W1 = w[1], W2 = w[2], W3 = w[3];
+                    const unsigned A0 = __funnelshift_r(W0, W1, s8), A1 = __funnelshift_r(W1, W2, s8), A2 = __funnelshift_r(W2, W3, s8);
+                    h[rr][0] = __dp4a(A0, K1, __dp4a(A1, K2, 0u));
+                    h[rr][1] = __dp4a(__funnelshift_r(A0, A1, 8), K1, __dp4a(__funnelshift_r(A1, A2, 8), K2, 0u));
+                    h[rr][2] = __dp4a(__funnelshift_r(A0, A1, 16), K1, __dp4a(__funnelshift_r(A1, A2, 16), K2, 0u));
+                    h[rr][3] = __dp4a(__funnelshift_r(A0, A1, 24), K1, __dp4a(__funnelshift_r(A1, A2, 24), K2, 0u));
+                }
             }
-            S.hp[it] = make_uint4(h[0][0] | (h[1][0] << 16), h[0][1] | (h[1][1] << 16), h[0][2] | (h[1][2] << 16), h[0][3] | (h[1][3] << 16));
+            __syncwarp();
+            if (on) S.raw4[e * HB_Q + q] = make_uint4(h[0][0] | (h[1][0] << 16), h[0][1] | (h[1][1] << 16), h[0][2] | (h[1][2] << 16), h[0][3] | (h[1][3] << 16));
         }
     }
     __syncwarp();
-    unsigned* bl = (unsigned*)S.raw4;   // the raw window is dead from here on (37 * 10 words <= 43 * 20)
+    const uint4* hp = S.raw4;
+    unsigned* bl = S.bl;
     // Vertical pass: lane = (group of four columns, third of the rows).  Output rows 2m and 2m+1 both read the row pairs
     // m .. m+3 — with taps {k0,k1 | k2,k3 | k4,k5 | k6,0} and {0,k0 | k1,k2 | k3,k4 | k5,k6} — so a four-pair window
     // slides down one pair per step, and an output is four dp2a starting from the rounding constant.
@@ -266,12 +273,12 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 8) describe_kernel(const __gr
         const unsigned CO = (18u << 8) | (34u << 16) | (48u << 24), CO2 = 56u | (48u << 8) | (34u << 16) | (18u << 24);
         uint4 wnd[4];                                   // circular: step t keeps pairs mb+t .. mb+t+3 in slots (t+j) % 4
 #pragma unroll
-        for (int k = 0; k < 3; k++) wnd[k] = S.hp[(mb + k) * HB_Q + q];
+        for (int k = 0; k < 3; k++) wnd[k] = hp[(mb + k) * HB_Q + q];
 #pragma unroll
         for (int t = 0; t < 7; t++) {
             const int m = mb + t;
             if (m < me) {
-                wnd[(t + 3) % 4] = S.hp[(m + 3) * HB_Q + q];
+                wnd[(t + 3) % 4] = hp[(m + 3) * HB_Q + q];
                 const uint4 p0 = wnd[t % 4], p1 = wnd[(t + 1) % 4], p2 = wnd[(t + 2) % 4], p3 = wnd[(t + 3) % 4];
                 const unsigned a0[4] = { p0.x, p0.y, p0.z, p0.w }, a1[4] = { p1.x, p1.y, p1.z, p1.w };
                 const unsigned a2[4] = { p2.x, p2.y, p2.z, p2.w }, a3[4] = { p3.x, p3.y, p3.z, p3.w };
