@@ -18,8 +18,14 @@
 //     roots in push_back order.
 // Tie rule for equal-size nodes: later-created first (DESIGN.md "canonical tie rule").
 #include "os1_internal.cuh"
+#include <cstdlib>
 
 #define QT_DONE 0xFFFFu
+// batches: four 512-thread CTAs per SM (32 registers per thread, no spills) — the kernel is bound by barriers and latency,
+// and at the compiler's own 56 registers only two CTAs were resident (0.44 -> 0.35 ms per 256 frames)
+#ifndef QT_MIN_CTAS_512
+#define QT_MIN_CTAS_512 4
+#endif
 #define QT_LEAF 0x80000000u
 
 namespace {
@@ -113,7 +119,7 @@ __device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
 }
 
 template <int QT_THREADS>
-__global__ void __launch_bounds__(QT_THREADS, 1024 / QT_THREADS) quadtree_kernel(const __grid_constant__ QtParams P)
+__global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_512 : 1) quadtree_kernel(const __grid_constant__ QtParams P)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
     const Geometry& g = P.g;
