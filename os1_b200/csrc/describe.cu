@@ -136,7 +136,7 @@ __device__ __forceinline__ void libm_sincosf(float y, float& sn, float& cs)
     cs = libm_sincosf_poly(xs, x2, flip, n ^ 1);
 }
 
-__global__ void __launch_bounds__(DESC_WARPS * 32, 9) describe_kernel(const __grid_constant__ DescParams P)
+__global__ void __launch_bounds__(DESC_WARPS * 32, 10) describe_kernel(const __grid_constant__ DescParams P)
 {
     __shared__ WarpSmem sm[DESC_WARPS];
     __shared__ IcTab ic;
