@@ -429,12 +429,12 @@ def run_ours(args, rank, world, local_rank):
     achieved = dom_bytes / (per_launch_ms[dom] * 1e-3) / 1e9
     whole = alg["total"] * B / (ms / args.steps * 1e-3) / 1e9
     # dram__bytes_read.sum + dram__bytes_write.sum per FRAME of this workload, from the ncu --set full capture of this
-    # very command (profiles/r01e_ncu_full_raw.csv, 256 frames per launch); both scale with the frames per launch
-    ncu_traffic_per_frame = {"pyramid": 716.97e6 / 256, "fast": 791.81e6 / 256, "quadtree": 227.48e6 / 256, "describe": 689.79e6 / 256}
+    # very command (profiles/r01f_ncu_full_raw.csv, 256 frames per launch); both scale with the frames per launch
+    ncu_traffic_per_frame = {"pyramid": 720.72e6 / 256, "fast": 792.31e6 / 256, "quadtree": 271.65e6 / 256, "describe": 688.46e6 / 256}
     roof = {"bound": "hbm", "kernel": names[dom] + "_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": ncu_traffic_per_frame[names[dom]] * B,
-            "traffic_source": "profiles/r01e_ncu_full_raw.csv (ncu --set full, same command, per launch)",
-            "note": "FAST is bound by the integer ALU pipe and instruction issue (ncu: ALU 79 % busy, issue 73 %, DRAM 4 %), not by HBM: see DESIGN.md section 4", "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)" if which == "measured" else "fallback 6650 GB/s",
+            "traffic_source": "profiles/r01f_ncu_full_raw.csv (ncu --set full, same command, per launch)",
+            "note": "FAST is bound by the integer ALU pipe and instruction issue (ncu: ALU 80 % busy, issue 73 %, DRAM 4 %), not by HBM: see DESIGN.md section 4", "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)" if which == "measured" else "fallback 6650 GB/s",
             "algorithmic_bytes_per_launch": dom_bytes,
             "kernel_ms_per_launch": {n: float(v) for n, v in zip(names, per_launch_ms)},
             "whole_step_achieved_gbs": whole, "whole_step_frac": whole / peak}
