@@ -74,6 +74,16 @@ __device__ void bitonic_sort(unsigned long long* a, int n, bool desc)
 {
     const int tid = threadIdx.x;
     if (n <= QT_THREADS) {
+        if ((tid & ~31) >= n) {
+            // a warp without keys only keeps the barrier count of the exchange steps below
+#pragma unroll 1
+            for (int k = 64; k <= n; k <<= 1)
+#pragma unroll 1
+                for (int j = k >> 1; j >= 32; j >>= 1) __syncthreads();
+            __syncthreads();
+            __syncthreads();
+            return;
+        }
         unsigned long long x = tid < n ? a[tid] : 0ull;
         int cur = 0;                        // which half of `a` the next shared-memory exchange writes
 #pragma unroll 1
