@@ -328,11 +328,11 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
 #pragma unroll
                     for (int q = 0; q < 4; q++) { uint32_t c = slotCnt[4 * j + q]; nz += (c > 0); mz += (c > 1); }
                 }
-                int tn, tm;
-                int en = block_scan_excl<QT_THREADS>(nz, warpSums, tn);
-                int em = block_scan_excl<QT_THREADS>(mz, warpSums, tm);
-                if (p < E) { nzCum[p] = carryN + en; mzCum[p] = carryM + em; }
-                carryN += tn; carryM += tm;
+                // one scan for both counts: each stays below 2^16 per trip (at most 4 children x QT_THREADS nodes)
+                int tot;
+                const int ex = block_scan_excl<QT_THREADS>(nz | (mz << 16), warpSums, tot);
+                if (p < E) { nzCum[p] = carryN + (ex & 0xFFFF); mzCum[p] = carryM + (ex >> 16); }
+                carryN += tot & 0xFFFF; carryM += tot >> 16;
             }
             if (tid == 0) { nzCum[E] = carryN; mzCum[E] = carryM; s_cut = E - 1; }
         }
