@@ -2,8 +2,8 @@
 // replaces src/MapPoint.cc:226-292: N x N DescriptorDistance matrix, median of every row, first row with the
 // least median).
 //
-// One warp per map point.  The point's N <= 256 observation descriptors are staged in shared memory; for row i the
-// lanes compute the distances to columns lane, lane+32, ... (at most eight per lane, kept in registers) and the
+// One warp per map point.  For row i the lanes compute the distances to columns lane, lane+32, ... (at most eight per
+// lane, kept in registers; up to 32 observations the descriptors themselves stay in registers and travel by shuffles) and the
 // median — element int(0.5*(N-1)) of the sorted row, MapPoint.cc:279 — is found without sorting: distances are
 // integers in [0, 256], so it is the smallest v with |{j : d_ij <= v}| >= k+1, located by a nine-step binary search
 // whose counts are ballots.  Rows are visited in ascending order and a row replaces the best only when its median is
@@ -36,10 +36,32 @@ __device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const u
     return __popc(sb) + __popc(sc) + 2 * __popc(sd) + 4 * __popc(cd);
 }
 
+__device__ __forceinline__ uint4 shfl4(const uint4& v, int src)
+{
+    return make_uint4(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src),
+                      __shfl_sync(0xffffffffu, v.w, src));
+}
+
+// smallest v in [0, 256] with |{d <= v}| >= need, d[0..T) per lane: nine ballot-counted steps
+template <int TMAX>
+__device__ __forceinline__ int median_of_row(const int (&d)[TMAX], int T, int need)
+{
+    int lo = 0, hi = 256;
+#pragma unroll 1
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        int c = 0;
+#pragma unroll
+        for (int t = 0; t < TMAX; t++)
+            if (t < T) c += __popc(__ballot_sync(0xffffffffu, d[t] <= mid));
+        if (c >= need) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
 __global__ void __launch_bounds__(DD_WARPS * 32) distinctive_kernel(const uint4* __restrict__ desc, const int* __restrict__ ptr, int npoints,
                                                                       int* __restrict__ bestIdx, int* __restrict__ bestMedian, int* status)
 {
-    __shared__ uint4 sd[DD_WARPS][2 * DD_MAXN];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int m = blockIdx.x * DD_WARPS + warp;
     if (m >= npoints) return;
@@ -52,32 +74,38 @@ __global__ void __launch_bounds__(DD_WARPS * 32) distinctive_kernel(const uint4*
         }
         return;
     }
-    uint4* D = sd[warp];
-    for (int i = lane; i < 2 * N; i += 32) D[i] = __ldg(desc + 2 * (long long)p0 + i);
-    __syncwarp();
-    const int T = (N + 31) >> 5;            // columns per lane
+    const uint4* D = desc + 2 * (long long)p0;
     const int need = ((N - 1) >> 1) + 1;    // int(0.5*(N-1)) + 1 values must be <= the median
     int best = INT_MAX, bi = 0;
+    if (N <= 32) {
+        // the usual case (a map point is seen from a handful of keyframes): lane j keeps descriptor j in registers, row i
+        // reaches the others by shuffles — no shared memory, no reloads
+        uint4 c0 = make_uint4(0, 0, 0, 0), c1 = c0;
+        if (lane < N) { c0 = __ldg(D + 2 * lane); c1 = __ldg(D + 2 * lane + 1); }
 #pragma unroll 1
-    for (int i = 0; i < N; i++) {
-        const uint4 a0 = D[2 * i], a1 = D[2 * i + 1];
-        int d[8];
-#pragma unroll
-        for (int t = 0; t < 8; t++) {
-            const int j = lane + 32 * t;
-            d[t] = (t < T && j < N) ? dist256(a0, a1, D[2 * j], D[2 * j + 1]) : 0x7FFF;
+        for (int i = 0; i < N; i++) {
+            const uint4 a0 = shfl4(c0, i), a1 = shfl4(c1, i);
+            int d[1];
+            d[0] = lane < N ? dist256(a0, a1, c0, c1) : 0x7FFF;
+            const int med = median_of_row<1>(d, 1, need);
+            if (med < best) { best = med; bi = i; }
         }
-        int lo = 0, hi = 256;
+    } else {
+        // up to 256 observations: columns lane, lane+32, ... straight from global memory (8 KB per point: L1 hits after the
+        // first row), at most eight distances per lane in registers
+        const int T = (N + 31) >> 5;
 #pragma unroll 1
-        while (lo < hi) {
-            const int mid = (lo + hi) >> 1;
-            int c = 0;
+        for (int i = 0; i < N; i++) {
+            const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+            int d[8];
 #pragma unroll
-            for (int t = 0; t < 8; t++)
-                if (t < T) c += __popc(__ballot_sync(0xffffffffu, d[t] <= mid));
-            if (c >= need) hi = mid; else lo = mid + 1;
+            for (int t = 0; t < 8; t++) {
+                const int j = lane + 32 * t;
+                d[t] = (t < T && j < N) ? dist256(a0, a1, __ldg(D + 2 * j), __ldg(D + 2 * j + 1)) : 0x7FFF;
+            }
+            const int med = median_of_row<8>(d, T, need);
+            if (med < best) { best = med; bi = i; }
         }
-        if (lo < best) { best = lo; bi = i; }
     }
     if (lane == 0) {
         bestIdx[m] = bi;
