@@ -10,6 +10,9 @@
  * by the caller (the reference calls its extractor from the tracker thread only, src/System.cc:64-66, and
  * the object is not re-entrant, src/ORBextractor.cc:979-986).  Distinct handles are independent and may
  * live on different GPUs.  There is no CPU fallback: without a CUDA device every call fails with OS1_E_CUDA.
+ *
+ * Current device: an entry point makes the GPU it works on current for the duration of the call and restores the
+ * calling thread's previous current device before it returns, on success and on failure alike.
  */
 #ifndef OS1_B200_H
 #define OS1_B200_H

@@ -25,7 +25,11 @@ struct DevBuf {
         if (p) cudaFree(p);
         p = nullptr; bytes = 0;
         cudaError_t e = cudaMalloc(&p, n);
-        if (e == cudaSuccess) { bytes = n; e = cudaMemset(p, 0, n); }     // slots a frame does not fill read as zero, never as stale data
+        // slots a frame does not fill read as zero, never as stale data.  The memset runs on the legacy stream, which the
+        // handle's non-blocking streams do not wait for: finish it here (set-up path) so that it can never land on top
+        // of an upload or a result queued right after
+        if (e == cudaSuccess) { bytes = n; e = cudaMemset(p, 0, n); }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(0);
         return e;
     }
     void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
@@ -85,6 +89,11 @@ int cuda_fail(os1_orb* h, cudaError_t e, const char* what)
     cudaGetLastError();
     return fail(h, OS1_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 }
+#define CKD(call, what)                                                       \
+    do {                                                                      \
+        cudaError_t _e = (call);                                              \
+        if (_e != cudaSuccess) { drain(); return cuda_fail(h, _e, what); }    \
+    } while (0)
 #define CK(call, what)                                          \
     do {                                                        \
         cudaError_t _e = (call);                                \
@@ -128,6 +137,23 @@ short sat_short(float v)
 
 // lets the other translation units of the library report through os1_last_error(NULL)
 void os1_internal_set_error(const char* msg) { t_err = msg ? msg : ""; }
+
+cudaError_t os1_optin_smem(const void* kernel)
+{
+    static std::mutex mu;
+    static std::vector<std::pair<const void*, int> > done;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(mu);
+    for (const auto& d : done)
+        if (d.first == kernel && d.second == dev) return cudaSuccess;
+    int optin = 0;
+    e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+    if (e == cudaSuccess) done.push_back(std::make_pair(kernel, dev));
+    return e;
+}
 
 // cv::resize INTER_LINEAR taps of one axis: first/second source index (already clamped
 // the way cv::resize clamps them on that axis) and the two 11-bit coefficients.
@@ -300,6 +326,10 @@ int build_geometry(os1_orb* h, int rows, int cols)
             os1_pyramid_plan_destroy(h->planBig); h->planBig = nullptr;
         }
     }
+    CK(os1_describe_init(), "describe tables");
+    // the table uploads above are pageable-memory copies on the legacy stream; the handle's streams are non-blocking and
+    // would not wait for them
+    CK(cudaStreamSynchronize(0), "sync after table uploads");
     h->haveGeom = true;
     h->batchCap = 0;
     return OS1_OK;
@@ -307,7 +337,6 @@ int build_geometry(os1_orb* h, int rows, int cols)
 
 int ensure(os1_orb* h, int rows, int cols, int nframes)
 {
-    CK(cudaSetDevice(h->device), "cudaSetDevice");
     if (!h->haveGeom || h->geom.rows != rows || h->geom.cols != cols) {
         if (h->haveGeom) CK(cudaStreamSynchronize(h->stream), "sync before re-planning");
         if (h->latExec) { cudaGraphExecDestroy(h->latExec); h->latExec = nullptr; }
@@ -334,6 +363,7 @@ int ensure(os1_orb* h, int rows, int cols, int nframes)
         // that the latency path fetches everything with ONE device-to-host copy
         CK(h->status.ensure(64 + (size_t)g.kpCapPerFrame * (sizeof(os1_kp_dev) + 32)), "cudaMalloc(status + single-frame outputs)");
         CK(cudaMemset(h->status.p, 0, 64), "cudaMemset(status)");
+        CK(cudaStreamSynchronize(0), "sync after cudaMemset(status)");
         CK(h->outKp.ensure(B * g.kpCapPerFrame * sizeof(os1_kp_dev)), "cudaMalloc(keypoints)");
         CK(h->outDesc.ensure(B * g.kpCapPerFrame * 32), "cudaMalloc(descriptors)");
         CK(h->outCount.ensure(B * 4), "cudaMalloc(counts)");
@@ -429,7 +459,8 @@ int os1_orb_create(os1_orb** out, int nfeatures, float scaleFactor, int nlevels,
         delete h;
         return fail(nullptr, OS1_E_UNSUPPORTED, "os1_orb_create: too many features in one pyramid level (the quadtree state of a level must fit one CTA's shared memory: about 2300)");
     }
-    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) {
+    DeviceScope _ds(device);
+    if ((e = _ds.err) != cudaSuccess || (e = cudaStreamCreateWithFlags(&h->ownStream, cudaStreamNonBlocking)) != cudaSuccess) {
         delete h;
         return cuda_fail(nullptr, e, "os1_orb_create");
     }
@@ -441,7 +472,7 @@ int os1_orb_create(os1_orb** out, int nfeatures, float scaleFactor, int nlevels,
 int os1_orb_destroy(os1_orb* h)
 {
     if (!h) return OS1_OK;
-    cudaSetDevice(h->device);
+    DeviceScope _ds(h->device);
     cudaStreamSynchronize(h->stream);
     if (h->latExec) cudaGraphExecDestroy(h->latExec);
     if (h->plan) os1_pyramid_plan_destroy(h->plan);
@@ -502,6 +533,7 @@ int os1_orb_reserve(os1_orb* h, int rows, int cols, int max_frames)
 {
     if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
     if (rows <= 0 || cols <= 0 || max_frames <= 0) return fail(h, OS1_E_INVALID, "os1_orb_reserve: bad size");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     return ensure(h, rows, cols, max_frames);
 }
 
@@ -517,7 +549,7 @@ int os1_orb_launches_per_call(const os1_orb*) { return 4; }
 int os1_orb_set_timing(os1_orb* h, int enable)
 {
     if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
-    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     if (enable && !h->ev[0])
         for (int i = 0; i < 5; i++) CK(cudaEventCreate(&h->ev[i]), "cudaEventCreate");
     h->timing = enable != 0;
@@ -528,7 +560,7 @@ int os1_orb_get_stage_times(os1_orb* h, float* ms4)
 {
     if (!h || !ms4) return fail(h, OS1_E_INVALID, "os1_orb_get_stage_times: NULL argument");
     if (!h->timing || !h->ev[0]) return fail(h, OS1_E_INVALID, "os1_orb_get_stage_times: timing is off");
-    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     CK(cudaEventSynchronize(h->ev[4]), "cudaEventSynchronize");
     for (int i = 0; i < 4; i++) CK(cudaEventElapsedTime(&ms4[i], h->ev[i], h->ev[i + 1]), "cudaEventElapsedTime");
     return OS1_OK;
@@ -537,7 +569,7 @@ int os1_orb_get_stage_times(os1_orb* h, float* ms4)
 int os1_orb_synchronize(os1_orb* h)
 {
     if (!h) return fail(nullptr, OS1_E_INVALID, "NULL handle");
-    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     if (!h->status.p) { CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize"); return OS1_OK; }
     CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "read status");
     CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
@@ -552,6 +584,7 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     if (!kp || !desc || !counts || cap_per_frame <= 0) return fail(h, OS1_E_INVALID, "os1_orb_extract_batch: NULL output or zero capacity");
     if (step < (size_t)cols || (nframes > 1 && frame_stride < step * (size_t)(rows - 1) + cols))
         return fail(h, OS1_E_INVALID, "os1_orb_extract_batch: step/frame_stride smaller than the image");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     int rc = ensure(h, rows, cols, nframes);
     if (rc) return rc;
     const Geometry& g = h->geom;
@@ -572,7 +605,10 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
         uint8_t* dst = slab + (long long)f0 * g.slabBytes + L0.off;
         if ((size_t)L0.pitch == step) {
             // same row pitch on both sides: a frame is one contiguous run, the batch a 2-D copy of long rows
-            return cudaMemcpy2DAsync(dst, (size_t)g.slabBytes, src, frame_stride, (size_t)(rows - 1) * step + cols, n, inKind, st);
+            // (a single frame needs no frame stride: whatever the caller passed there is not used as a pitch)
+            const size_t run = (size_t)(rows - 1) * step + cols;
+            if (n == 1) return cudaMemcpyAsync(dst, src, run, inKind, st);
+            return cudaMemcpy2DAsync(dst, (size_t)g.slabBytes, src, frame_stride, run, n, inKind, st);
         }
         if (n > 1 && frame_stride % step == 0 && g.slabBytes % L0.pitch == 0) {
             cudaMemcpy3DParms p;
@@ -613,6 +649,7 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
         bool done = false;
         if (graphOk && h->latExec) {
             CK(cudaGraphLaunch(h->latExec, h->stream), "cudaGraphLaunch");
+            h->lastFrames = 1; h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch;    // (what run_pipeline records)
             done = true;
         } else if (graphOk && ++h->latCalls >= 3) {
             // (the first calls run plainly: lazily initialised tables and function attributes must exist before a capture)
@@ -653,14 +690,15 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
 
     // ---- batches with host buffers: chunks flow through upload -> kernels -> download on three streams, so the PCIe
     // copies of neighbouring chunks hide behind the kernels of the current one ----------------------------------------------
-    int chunk = 16;
-    if (const char* e = getenv("OS1_CHUNK")) chunk = std::max(1, atoi(e));
+    // (tuning knobs are read once per process)
+    static const int envChunk = getenv("OS1_CHUNK") ? std::max(1, atoi(getenv("OS1_CHUNK"))) : 0;
+    static const int envRamp0 = getenv("OS1_RAMP0") ? std::max(1, atoi(getenv("OS1_RAMP0"))) : 0;
+    static const int envRampPct = getenv("OS1_RAMPPCT") ? std::max(100, atoi(getenv("OS1_RAMPPCT"))) : 0;
+    const int chunk = envChunk ? envChunk : 16;
     // chunk boundaries: a geometric ramp.  The upload of chunk c+1 hides behind the kernels of chunk c only while it is
     // not longer than them, so chunks grow by less than the kernel-time / upload-time ratio per frame (1.31 at 720p over
     // PCIe 5 x16); the kernels then start after the upload of a few frames and never starve again
-    int ramp0 = std::max(1, chunk / 8), rampPct = 125;
-    if (const char* e = getenv("OS1_RAMP0")) ramp0 = std::max(1, atoi(e));
-    if (const char* e = getenv("OS1_RAMPPCT")) rampPct = std::max(100, atoi(e));
+    const int ramp0 = envRamp0 ? envRamp0 : std::max(1, chunk / 8), rampPct = envRampPct ? envRampPct : 125;
     std::vector<int> cuts(1, 0);
     for (int f = 0, sz = std::min(ramp0, chunk); f < nframes;) {
         f = std::min(nframes, f + sz);
@@ -692,38 +730,44 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     }
     const size_t kpRow = (size_t)dCap * sizeof(os1_kp_dev), dRow = (size_t)dCap * 32;
     const int copyCap = std::min(dCap, cap_per_frame);
+    // a failure half way through leaves copies queued that write into the caller's buffers: wait for them before returning
+    auto drain = [&]() {
+        cudaStreamSynchronize(h->inStream); cudaStreamSynchronize(h->outStream); cudaStreamSynchronize(h->stream);
+        for (int i = 0; i < 3; i++) if (h->altStream[i]) cudaStreamSynchronize(h->altStream[i]);
+        cudaGetLastError();
+    };
     for (int c = 0; c < nchunks; c++) {
         const int f0 = cuts[c], n = cuts[c + 1] - cuts[c];
         cudaStream_t cs = (alt && c % (nAlt + 1)) ? h->altStream[c % (nAlt + 1) - 1] : h->stream;
         if (!direct) {
-            CK(stage_in(f0, n, frames_on_device ? cs : h->inStream), "upload frames");
+            CKD(stage_in(f0, n, frames_on_device ? cs : h->inStream), "upload frames");
             if (!frames_on_device) {
-                CK(cudaEventRecord(h->chunkEv[2 * c], h->inStream), "cudaEventRecord");
-                CK(cudaStreamWaitEvent(cs, h->chunkEv[2 * c], 0), "cudaStreamWaitEvent");
+                CKD(cudaEventRecord(h->chunkEv[2 * c], h->inStream), "cudaEventRecord");
+                CKD(cudaStreamWaitEvent(cs, h->chunkEv[2 * c], 0), "cudaStreamWaitEvent");
             }
         }
         rc = run_pipeline(h, lvl0, lvl0Stride, lvl0Pitch, n, dKp + (size_t)f0 * dCap, dDesc + (size_t)f0 * dRow, dCap, dCnt + f0, f0, cs);
-        if (rc) return rc;
+        if (rc) { drain(); return rc; }
         if (!out_on_device) {
-            CK(cudaEventRecord(h->chunkEv[2 * c + 1], cs), "cudaEventRecord");
-            CK(cudaStreamWaitEvent(h->outStream, h->chunkEv[2 * c + 1], 0), "cudaStreamWaitEvent");
+            CKD(cudaEventRecord(h->chunkEv[2 * c + 1], cs), "cudaEventRecord");
+            CKD(cudaStreamWaitEvent(h->outStream, h->chunkEv[2 * c + 1], 0), "cudaStreamWaitEvent");
             // straight into the caller's slabs (row = frame; pitches differ when the caller's capacity does)
-            CK(cudaMemcpy2DAsync(kp + (size_t)f0 * cap_per_frame, (size_t)cap_per_frame * sizeof(os1_keypoint), dKp + (size_t)f0 * dCap, kpRow,
+            CKD(cudaMemcpy2DAsync(kp + (size_t)f0 * cap_per_frame, (size_t)cap_per_frame * sizeof(os1_keypoint), dKp + (size_t)f0 * dCap, kpRow,
                                  (size_t)copyCap * sizeof(os1_keypoint), n, cudaMemcpyDeviceToHost, h->outStream), "download keypoints");
-            CK(cudaMemcpy2DAsync(desc + (size_t)f0 * cap_per_frame * 32, (size_t)cap_per_frame * 32, dDesc + (size_t)f0 * dRow, dRow,
+            CKD(cudaMemcpy2DAsync(desc + (size_t)f0 * cap_per_frame * 32, (size_t)cap_per_frame * 32, dDesc + (size_t)f0 * dRow, dRow,
                                  (size_t)copyCap * 32, n, cudaMemcpyDeviceToHost, h->outStream), "download descriptors");
-            CK(cudaMemcpyAsync(counts + f0, dCnt + f0, (size_t)n * 4, cudaMemcpyDeviceToHost, h->outStream), "download counts");
+            CKD(cudaMemcpyAsync(counts + f0, dCnt + f0, (size_t)n * 4, cudaMemcpyDeviceToHost, h->outStream), "download counts");
         }
     }
     if (alt) {       // join: everything queued on the second stream is ordered before what follows on the handle's stream
         for (int i = 0; i < nAlt; i++) {
-            CK(cudaEventRecord(h->altEv[i], h->altStream[i]), "cudaEventRecord");
-            CK(cudaStreamWaitEvent(h->stream, h->altEv[i], 0), "cudaStreamWaitEvent");
+            CKD(cudaEventRecord(h->altEv[i], h->altStream[i]), "cudaEventRecord");
+            CKD(cudaStreamWaitEvent(h->stream, h->altEv[i], 0), "cudaStreamWaitEvent");
         }
     }
-    CK(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
-    CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
-    if (!out_on_device) CK(cudaStreamSynchronize(h->outStream), "cudaStreamSynchronize");
+    CKD(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
+    CKD(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
+    if (!out_on_device) CKD(cudaStreamSynchronize(h->outStream), "cudaStreamSynchronize");
     rc = check_status(h, h->hostStatus[0]);
     if (rc) return rc;
     if (!out_on_device)
@@ -753,7 +797,7 @@ int os1_orb_get_pyramid_level(os1_orb* h, int frame, int level, uint8_t* out_hos
 {
     if (!h || !h->haveGeom || level < 0 || level >= h->nlevels || frame < 0 || frame >= h->lastFrames || !out_host)
         return fail(h, OS1_E_INVALID, "os1_orb_get_pyramid_level: bad argument");
-    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     const LevelGeom& L = h->geom.lv[level];
     const uint8_t* src; size_t pitch;
     if (level == 0) { src = h->lastLvl0 + (long long)frame * h->lastLvl0Stride; pitch = h->lastLvl0Pitch; }
@@ -777,7 +821,7 @@ int os1_orb_get_candidates(os1_orb* h, int frame, int level, int32_t* xys, int c
 {
     if (!h || !h->haveGeom || level < 0 || level >= h->nlevels || frame < 0 || frame >= h->lastFrames || !n)
         return fail(h, OS1_E_INVALID, "os1_orb_get_candidates: bad argument");
-    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
     uint32_t cnt = 0;
     CK(cudaMemcpy(&cnt, (uint32_t*)h->candCount.p + (size_t)frame * h->nlevels + level, 4, cudaMemcpyDeviceToHost), "download count");
@@ -791,7 +835,7 @@ int os1_orb_get_level_keypoints(os1_orb* h, int frame, int level, int32_t* xys, 
 {
     if (!h || !h->haveGeom || level < 0 || level >= h->nlevels || frame < 0 || frame >= h->lastFrames || !n)
         return fail(h, OS1_E_INVALID, "os1_orb_get_level_keypoints: bad argument");
-    CK(cudaSetDevice(h->device), "cudaSetDevice");
+    DeviceScope _ds(h->device); CK(_ds.err, "cudaSetDevice");
     CK(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
     uint32_t cnt = 0;
     CK(cudaMemcpy(&cnt, (uint32_t*)h->lvCount.p + (size_t)frame * h->nlevels + level, 4, cudaMemcpyDeviceToHost), "download count");
@@ -832,7 +876,7 @@ int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t
     if (nA < 0 || nB < 0 || (nA > 0 && (!A || !best_idx || !best_dist || !second_dist)) || (nB > 0 && !B))
         return fail(nullptr, OS1_E_INVALID, "os1_hamming_knn2: bad argument");
     if (nA == 0) return OS1_OK;
-    CK(cudaSetDevice(device), "cudaSetDevice (no CPU fallback)");
+    DeviceScope _ds(device); CK(_ds.err, "cudaSetDevice (no CPU fallback)");
     cudaStream_t s = (cudaStream_t)cuda_stream;
     const int nSplit = os1_hamming_splits(nA, nB, sm_count(device));
     uint64_t* scratch = nullptr;
@@ -870,7 +914,7 @@ int os1_hamming_window(const uint8_t* A, int nA, const uint8_t* B, int nB, const
     if (nA < 0 || nB < 0 || (nA > 0 && (!A || !ptr || !best_idx || !best_dist || !second_dist)))
         return fail(nullptr, OS1_E_INVALID, "os1_hamming_window: bad argument");
     if (nA == 0) return OS1_OK;
-    CK(cudaSetDevice(device), "cudaSetDevice (no CPU fallback)");
+    DeviceScope _ds(device); CK(_ds.err, "cudaSetDevice (no CPU fallback)");
     cudaStream_t s = (cudaStream_t)cuda_stream;
     if (on_device) {
         cudaError_t e = os1_launch_hamming_window(A, nA, B, ptr, cand, best_idx, best_dist, second_dist, s);

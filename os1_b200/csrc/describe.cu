@@ -11,6 +11,7 @@
 // rotated taps all read it from there.  No FMA contraction anywhere in the float path (x86 reference build has
 // none); cos/sin follow glibc's cosf/sinf algorithm (see libm_sincosf).
 #include "os1_internal.cuh"
+#include <mutex>
 #include <cmath>
 #include <cfloat>
 
@@ -331,47 +332,58 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, 10) describe_kernel(const __g
 
 } // namespace
 
+// umax exactly as the reference builds it (ORBextractor.cc:486-501)
+static void build_umax(int* umax)
+{
+    const int HP = 15;
+    int v, v0, vmax = (int)floor(HP * sqrt(2.f) / 2 + 1);
+    int vmin = (int)ceil(HP * sqrt(2.f) / 2);
+    const double hp2 = HP * HP;
+    for (v = 0; v <= vmax; ++v) umax[v] = (int)lrint(sqrt(hp2 - v * v));
+    for (v = HP, v0 = 0; v >= vmin; --v) {
+        while (umax[v0] == umax[v0 + 1]) ++v0;
+        umax[v] = v0;
+        ++v0;
+    }
+}
+
+// Per-device constant table of the intensity-centroid pass.  Called from handle set-up (never from inside a launch
+// sequence, which may be under stream capture), once per device, under a lock; synchronous.
+cudaError_t os1_describe_init()
+{
+    static std::mutex mu;
+    static bool filled[64] = { false };
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(mu);
+    if (filled[dev]) return cudaSuccess;
+    int umax[16];
+    build_umax(umax);
+    IcTab t;
+    for (int av = 0; av < 16; av++)
+        for (int k = 0; k < 9; k++) {
+            int cu = 0; unsigned cm = 0;
+            for (int b = 0; b < 4; b++) {
+                const int u = 4 * (k + 1) + b - WIN_R;               // window column 4(k+1)+b  <->  patch offset u
+                if (u >= -umax[av] && u <= umax[av]) { cu |= (u & 0xFF) << (8 * b); cm |= 1u << (8 * b); }
+            }
+            t.cu[av][k] = cu; t.cm[av][k] = cm;
+        }
+    e = cudaMemcpyToSymbol(d_ic, &t, sizeof(t), 0, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(0);
+    if (e == cudaSuccess) filled[dev] = true;
+    return e;
+}
+
 cudaError_t os1_launch_describe(const Geometry& g, const DevPtrs& d, int nframes, os1_kp_dev* kp, uint8_t* desc, int capPerFrame,
                                 int* counts, cudaStream_t s)
 {
     static_assert(sizeof(DescParams) < 4000, "kernel parameter block too large");
     DescParams P;
     P.g = g; P.d = d; P.kp = kp; P.desc = desc; P.counts = counts; P.capPerFrame = capPerFrame;
-    // umax exactly as the reference builds it (ORBextractor.cc:486-501)
-    {
-        const int HP = 15;
-        int v, v0, vmax = (int)floor(HP * sqrt(2.f) / 2 + 1);
-        int vmin = (int)ceil(HP * sqrt(2.f) / 2);
-        const double hp2 = HP * HP;
-        for (v = 0; v <= vmax; ++v) P.umax[v] = (int)lrint(sqrt(hp2 - v * v));
-        for (v = HP, v0 = 0; v >= vmin; --v) {
-            while (P.umax[v0] == P.umax[v0 + 1]) ++v0;
-            P.umax[v] = v0;
-            ++v0;
-        }
-    }
-    {
-        static bool filled[64] = { false };
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (dev >= 0 && dev < 64 && !filled[dev]) {
-            IcTab t;
-            for (int av = 0; av < 16; av++)
-                for (int k = 0; k < 9; k++) {
-                    int cu = 0; unsigned cm = 0;
-                    for (int b = 0; b < 4; b++) {
-                        const int u = 4 * (k + 1) + b - WIN_R;               // window column 4(k+1)+b  <->  patch offset u
-                        if (u >= -P.umax[av] && u <= P.umax[av]) { cu |= (u & 0xFF) << (8 * b); cm |= 1u << (8 * b); }
-                    }
-                    t.cu[av][k] = cu; t.cm[av][k] = cm;
-                }
-            cudaError_t e = cudaMemcpyToSymbolAsync(d_ic, &t, sizeof(t), 0, cudaMemcpyHostToDevice, s);
-            if (e != cudaSuccess) return e;
-            e = cudaStreamSynchronize(s);            // `t` lives on this stack frame
-            if (e != cudaSuccess) return e;
-            filled[dev] = true;
-        }
-    }
+    build_umax(P.umax);
     volatile float R = (float)(180.0 / 3.1415926535897932384626433832795);
     volatile float t;
     t = 0.9997878412794807f * R; P.p1 = t;

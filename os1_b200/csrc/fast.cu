@@ -432,7 +432,7 @@ template <int PW>
 static cudaError_t launch_fast_pw(const FastParams& P, size_t smem, dim3 grid, cudaStream_t s)
 {
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(fast_kernel<PW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = os1_optin_smem((const void*)fast_kernel<PW>);
         if (e != cudaSuccess) return e;
     }
     fast_kernel<PW><<<grid, FAST_THREADS, smem, s>>>(P);

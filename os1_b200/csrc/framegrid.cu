@@ -153,7 +153,7 @@ cudaError_t run_device(const os1_kp_dev* kp, int n, GridGeom G, const float* qx,
     if (e == cudaSuccess) e = cudaMallocAsync((void**)&cnt, (size_t)std::max(nq, 1) * 4, s);
     if (e == cudaSuccess) {
         const size_t smem = (size_t)n2 * 4;
-        if (smem > 48 * 1024) e = cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (smem > 48 * 1024) e = os1_optin_smem((const void*)grid_build_kernel);
         if (e == cudaSuccess) grid_build_kernel<<<1, FG_THREADS, smem, s>>>(kp, n, G, n2, cellStart, gridIdx);
         if (nq > 0) {
             area_count_kernel<<<(nq + 127) / 128, 128, 0, s>>>(kp, cellStart, gridIdx, G, qx, qy, qr, qmin, qmax, nq, cnt);
@@ -187,7 +187,7 @@ extern "C" int os1_features_in_area(const os1_keypoint* kp, int n, float min_x, 
     G.invW = (float)GRID_COLS / (max_x - min_x);          // mfGridElementWidthInv   Frame.cc:99
     G.invH = (float)GRID_ROWS / (max_y - min_y);
     cudaStream_t s = (cudaStream_t)cuda_stream;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceScope _ds(device); cudaError_t e = _ds.err;
     if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_features_in_area: cudaSetDevice failed (no CPU fallback)"); return OS1_E_CUDA; }
     if (on_device) {
         e = run_device((const os1_kp_dev*)kp, n, G, qx, qy, qr, q_min_level, q_max_level, nq, ptr, cand, cand_cap, s);
@@ -277,7 +277,7 @@ extern "C" int os1_undistort_keypoints(const os1_keypoint* kp, int n, const floa
     }
     if (n == 0) return OS1_OK;
     cudaStream_t s = (cudaStream_t)cuda_stream;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceScope _ds(device); cudaError_t e = _ds.err;
     if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_undistort_keypoints: cudaSetDevice failed (no CPU fallback)"); return OS1_E_CUDA; }
     const bool identity = mode == 0 && (ndist == 0 || dist[0] == 0.0f);        // Frame.cc:288-292
     CamParams C;
@@ -307,7 +307,10 @@ extern "C" int os1_undistort_keypoints(const os1_keypoint* kp, int n, const floa
 // Frame::ComputeImageBounds (src/Frame.cc:322-353): the four image corners through the same undistortion
 extern "C" int os1_image_bounds(int cols, int rows, const float* K4, const float* dist, int ndist, int mode, float* bounds4, int device)
 {
-    if (!bounds4 || !K4 || cols <= 0 || rows <= 0) { os1_internal_set_error("os1_image_bounds: bad argument"); return OS1_E_INVALID; }
+    if (!bounds4 || !K4 || cols <= 0 || rows <= 0 || (mode != 0 && mode != 1) || ndist < 0 || ndist > 14 || (mode == 0 && ndist > 0 && !dist)) {
+        os1_internal_set_error("os1_image_bounds: bad argument (NULL pointer, mode outside {0,1}, or ndist outside 0..14)");
+        return OS1_E_INVALID;
+    }
     if (mode == 0 && (ndist == 0 || dist[0] == 0.0f)) {
         bounds4[0] = 0.0f; bounds4[1] = (float)cols; bounds4[2] = 0.0f; bounds4[3] = (float)rows;
         return OS1_OK;

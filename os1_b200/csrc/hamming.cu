@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(HM_ROWS) hamming_pairs_kernel(const uint4* __r
 {
     __shared__ uint4 tile[HM_TILE * 2];
     const int2 pr = pairs[blockIdx.y];
-    const int nA = counts[pr.x], nB = counts[pr.y];
+    const int nA = min(counts[pr.x], cap), nB = min(counts[pr.y], cap);      // a count above the slab's capacity is clamped, never followed out of bounds
     if ((int)(blockIdx.x * HM_ROWS) >= nA) return;
     const uint4* A = desc + (long long)pr.x * cap * 2;
     const uint4* B = desc + (long long)pr.y * cap * 2;
@@ -271,7 +271,7 @@ extern "C" int os1_hamming_knn2_noalloc(const uint8_t* A, int nA, const uint8_t*
         return OS1_E_CAPACITY;
     }
     if (nA == 0) return OS1_OK;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceScope _ds(device); cudaError_t e = _ds.err;
     if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_hamming_knn2_noalloc: cudaSetDevice failed (no CPU fallback)"); return OS1_E_CUDA; }
     NoAllocDevice dev;
     {

@@ -127,7 +127,7 @@ extern "C" int os1_distinctive_descriptors(const uint8_t* desc, const int32_t* p
     if (npoints < 0 || (npoints > 0 && (!ptr || !best_idx))) return set_err("os1_distinctive_descriptors: bad argument", OS1_E_INVALID);
     if (npoints == 0) return OS1_OK;
     cudaStream_t s = (cudaStream_t)cuda_stream;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceScope _ds(device); cudaError_t e = _ds.err;
     if (e != cudaSuccess) { cudaGetLastError(); return set_err("os1_distinctive_descriptors: cudaSetDevice failed (no CPU fallback)", OS1_E_CUDA); }
     const int grid = (npoints + DD_WARPS - 1) / DD_WARPS;
     int* dStatus = nullptr;

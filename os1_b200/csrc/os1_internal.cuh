@@ -86,6 +86,23 @@ struct DevPtrs {
 // cv::KeyPoint layout (28 bytes): pt.x pt.y size angle response octave class_id
 struct os1_kp_dev { float x, y, size, angle, response; int octave, class_id; };
 
+// Makes `device` current for the lifetime of the object and restores the caller's current device afterwards: the library
+// never leaves a host thread pointed at a different GPU than it came in with.
+struct DeviceScope {
+    int prev = -1;
+    cudaError_t err;
+    explicit DeviceScope(int device)
+    {
+        err = cudaGetDevice(&prev);
+        if (err != cudaSuccess) { prev = -1; cudaGetLastError(); }
+        if (prev == device) { prev = -1; err = cudaSuccess; }
+        else err = cudaSetDevice(device);
+    }
+    ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceScope(const DeviceScope&) = delete;
+    DeviceScope& operator=(const DeviceScope&) = delete;
+};
+
 // ---- launchers (one per kernel family) -----------------------------------------------------------
 struct PyramidPlan;   // host-side tile tables (pyramid.cu)
 PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH);
@@ -95,6 +112,7 @@ cudaError_t os1_launch_pyramid(PyramidPlan*, const Geometry& g, const DevPtrs& d
 cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
 bool os1_quadtree_fits(int maxQuota, int maxCells, int maxIni);       // the per-level state fits one CTA's shared memory
 cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes, int maxQuota, int maxCells, cudaStream_t s);
+cudaError_t os1_describe_init();      // per-device constant table; call with the device current, outside any capture
 cudaError_t os1_launch_describe(const Geometry& g, const DevPtrs& d, int nframes, os1_kp_dev* kp, uint8_t* desc, int capPerFrame,
                                 int* counts, cudaStream_t s);
 // Hamming: nSplit partitions of B; scratch holds nSplit * nA uint2 partials
@@ -105,5 +123,9 @@ cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B
                                       int* bestDist, int* secondDist, cudaStream_t s);
 cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s);
 void os1_internal_set_error(const char* msg);
+// Raises a kernel's dynamic shared-memory limit to the device's opt-in maximum, once per (kernel, device) and under a
+// lock, so that handles with different tile sizes — and host threads launching at the same time — never lower or race
+// on a limit another launch relies on (the attribute belongs to the function, not to a handle).
+cudaError_t os1_optin_smem(const void* kernel);
 cudaError_t os1_launch_hamming_pairs(const uint8_t* desc, const int* counts, int cap, const int* pairs, int npairs, int* bestIdx, int* bestDist,
                                      int* secondDist, int* accepted, float nnratio, int thLow, cudaStream_t s);

@@ -220,6 +220,7 @@ struct PyramidPlan {
     int4* d_qtab = nullptr;
     int4* d_ytab = nullptr;
     bool tapsFit = true;       // every group of four columns finds its eight taps in three consecutive source words
+    cudaError_t cudaErr = cudaSuccess;      // first failure of a table allocation / upload
     PyrParams prm;
     int boxW, boxH;
     size_t smemBytes;
@@ -280,18 +281,20 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
     std::vector<int> mw, mh;
     build_axis(g, false, tileW, P->ntx, xt, mw);
     build_axis(g, true, tileH, P->nty, yt, mh);
-    cudaMalloc(&P->d_xt, xt.size() * sizeof(int4));
-    cudaMalloc(&P->d_yt, yt.size() * sizeof(int4));
-    cudaMemcpy(P->d_xt, xt.data(), xt.size() * sizeof(int4), cudaMemcpyHostToDevice);
-    cudaMemcpy(P->d_yt, yt.data(), yt.size() * sizeof(int4), cudaMemcpyHostToDevice);
+    auto upload = [&](int4*& dptr, const std::vector<int4>& v) {
+        cudaError_t e = cudaMalloc(&dptr, v.size() * sizeof(int4));
+        if (e == cudaSuccess) e = cudaMemcpy(dptr, v.data(), v.size() * sizeof(int4), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess && P->cudaErr == cudaSuccess) { P->cudaErr = e; cudaGetLastError(); }
+    };
+    upload(P->d_xt, xt);
+    upload(P->d_yt, yt);
     std::vector<int4> xg(xt.size());
     for (size_t i = 0; i < xt.size(); i++) {
         const int ng = std::max(1, ((xt[i].y + 3) >> 2) - ((xt[i].x & ~3) >> 2));
         const int nb = std::max(1, 256 / ng);
         xg[i] = make_int4(ng, (1 << 24) / ng + 1, nb, (1 << 24) / nb + 1);
     }
-    cudaMalloc(&P->d_xg, xg.size() * sizeof(int4));
-    cudaMemcpy(P->d_xg, xg.data(), xg.size() * sizeof(int4), cudaMemcpyHostToDevice);
+    upload(P->d_xg, xg);
     PyrParams& p = P->prm;
     memset(&p, 0, sizeof(p));
     p.nlevels = g.nlevels; p.ntx = P->ntx; p.nty = P->nty;
@@ -336,12 +339,10 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
             for (int y = 0; y < g.lv[l].h; y++) yt4.push_back(make_int4(s0[y], s1[y], (int)c0[y] << 12, (int)c1[y] << 12));
         }
         if (yt4.empty()) yt4.push_back(make_int4(0, 0, 0, 0));
-        cudaMalloc(&P->d_ytab, yt4.size() * sizeof(int4));
-        cudaMemcpy(P->d_ytab, yt4.data(), yt4.size() * sizeof(int4), cudaMemcpyHostToDevice);
+        upload(P->d_ytab, yt4);
         p.ytab = P->d_ytab;
         if (q.empty()) q.push_back(make_int4(0, 0, 0, 0));
-        cudaMalloc(&P->d_qtab, q.size() * sizeof(int4));
-        cudaMemcpy(P->d_qtab, q.data(), q.size() * sizeof(int4), cudaMemcpyHostToDevice);
+        upload(P->d_qtab, q);
         p.qtab = P->d_qtab;
     }
     P->boxW = (mw[0] + 15) & ~15;
@@ -368,17 +369,12 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         fn = nullptr;
     }
     P->encode = (decltype(P->encode))fn;
-    if (P->smemBytes > 48 * 1024)
-    {
-        cudaFuncSetAttribute(pyramid_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smemBytes);
-        cudaFuncSetAttribute(pyramid_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P->smemBytes);
-    }
     return P;
 }
 
 bool os1_pyramid_plan_ok(const PyramidPlan* P)
 {
-    return P && P->encode && P->tapsFit && P->boxW <= 256 && P->boxH <= 256 && P->smemBytes <= 200 * 1024;
+    return P && P->cudaErr == cudaSuccess && P->encode && P->tapsFit && P->boxW <= 256 && P->boxH <= 256 && P->smemBytes <= 200 * 1024;
 }
 
 void os1_pyramid_plan_destroy(PyramidPlan* P)
@@ -405,6 +401,10 @@ cudaError_t os1_launch_pyramid(PyramidPlan* P, const Geometry& g, const DevPtrs&
     dim3 grid(P->ntx, P->nty, nframes), block(32, 8);
     p.dbgLvl0 = d.lvl0; p.dbgStride = d.lvl0FrameStride; p.dbgPitch = d.lvl0Pitch; p.dbgW = g.cols; p.dbgH = g.rows;
     static const bool noTma = getenv("OS1_DEBUG_NOTMA") != nullptr;
+    if (P->smemBytes > 48 * 1024) {
+        cudaError_t e = os1_optin_smem(noTma ? (const void*)pyramid_kernel<false> : (const void*)pyramid_kernel<true>);
+        if (e != cudaSuccess) return e;
+    }
     if (noTma) pyramid_kernel<false><<<grid, block, P->smemBytes, s>>>(tmap, p);
     else pyramid_kernel<true><<<grid, block, P->smemBytes, s>>>(tmap, p);
     return cudaGetLastError();

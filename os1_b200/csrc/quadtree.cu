@@ -477,13 +477,13 @@ cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes
     // few frames: the level-0 CTA is the critical path, give it 1024 threads; batches: 512 threads, two CTAs per SM
     if (nframes <= 4) {
         if (smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute(quadtree_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            cudaError_t e = os1_optin_smem((const void*)quadtree_kernel<1024>);
             if (e != cudaSuccess) return e;
         }
         quadtree_kernel<1024><<<grid, 1024, smem, s>>>(P);
     } else {
         if (smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute(quadtree_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            cudaError_t e = os1_optin_smem((const void*)quadtree_kernel<512>);
             if (e != cudaSuccess) return e;
         }
         quadtree_kernel<512><<<grid, 512, smem, s>>>(P);

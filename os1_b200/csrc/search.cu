@@ -64,7 +64,7 @@ int os1_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, int nB, const in
 {
     if (nA <= 0) return OS1_OK;
     cudaStream_t s = (cudaStream_t)cuda_stream;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceScope _ds(device); cudaError_t e = _ds.err;
     if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_hamming_csr: cudaSetDevice failed (no CPU fallback)"); return OS1_E_CUDA; }
     if (on_device) {
         e = os1_launch_hamming_csr(A, nA, B, ptr, cand, dist, s);
@@ -100,7 +100,7 @@ int os1_hamming_knn2_pairs(const uint8_t* desc, const int32_t* counts, int cap, 
 {
     if (npairs < 0 || cap <= 0 || (npairs > 0 && (!desc || !counts || !pairs))) { os1_internal_set_error("os1_hamming_knn2_pairs: bad argument"); return OS1_E_INVALID; }
     if (npairs == 0) return OS1_OK;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceScope _ds(device); cudaError_t e = _ds.err;
     if (e == cudaSuccess) e = os1_launch_hamming_pairs(desc, counts, cap, pairs, npairs, best_idx, best_dist, second_dist, accepted, nnratio, th_low,
                                                       (cudaStream_t)cuda_stream);
     if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_hamming_knn2_pairs: CUDA failure (no CPU fallback)"); return OS1_E_CUDA; }
