@@ -252,4 +252,33 @@ static inline void fast9_16(const uchar* img, int w, int h, size_t step, int thr
         }
 }
 
+// ---- undistortPoints(src, dst, K, dist, R = Mat(), P = K) ------------------------------------------------------
+// OpenCV's published iterative inverse of the Brown model: five fixed-point iterations, everything in double, then the
+// projection through P = K.  K4 = {fx, fy, cx, cy} (float entries widened), dist = k1,k2,p1,p2[,k3[,k4,k5,k6[,s1..s4]]].
+// Pinned against cv2.undistortPoints 4.13 for 4, 5 and 8 coefficients (tests/test_oracle_primitives.py).
+// Call sites: Frame.cc:307 (UndistortKeyPoints), :338 (ComputeImageBounds).
+static inline void undistort_points(const float* xy, int n, const float* K4, const float* dist, int ndist, float* out)
+{
+    const double fx = K4[0], fy = K4[1], cx = K4[2], cy = K4[3];
+    double k[14] = { 0 };
+    for (int i = 0; i < ndist && i < 14; i++) k[i] = dist[i];
+    const double ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < n; i++) {
+        double x = xy[2 * i], y = xy[2 * i + 1];
+        x = (x - cx) * ifx; y = (y - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = x0; y = y0; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = fx * x + 0.0 * y + cx, yy = 0.0 * x + fy * y + cy, ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        out[2 * i] = (float)(xx * ww); out[2 * i + 1] = (float)(yy * ww);
+    }
+}
+
 } // namespace cvx

@@ -6,6 +6,10 @@
   extract_*.npz  : keypoints + descriptors + per-level candidate counts produced by the UNMODIFIED reference
                    ORBextractor.cc (oracle/_ref/libos1_ref_canon.so, canonical tie rule) on seeded synthetic frames,
                    plus the count/difference seen with the stock glibc allocator build (libos1_ref.so).
+  matcher_<kind>.npz : outputs of the reference's own matcher / Frame / MapPoint function bodies (oracle/_ref/libos1_refmatch.so:
+                   ORBmatcher.cc, Frame.cc, MapPoint.cc sliced by path and compiled unmodified, oracle/refmatch/) on the seeded
+                   scenarios of oracle/matcher_cases.py, with a digest of the scenario inputs.
+  gemm in primitives.npz : cv2.gemm on 3x3 * 3x1 float matrices, the arithmetic behind `Rcw*x3Dw+tcw` (ORBmatcher.cc:1325).
 The frames themselves are regenerated from the seed by os1_b200/synth.py, so the fixtures stay small.
 """
 import os
@@ -47,6 +51,12 @@ def primitives():
         K = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]], np.float32)
         d["und_K_" + name] = np.array(K4, np.float32); d["und_D_" + name] = np.array(dist, np.float32)
         d["und_out_" + name] = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, np.array(dist, np.float32), None, K).reshape(-1, 2)
+    # cv::gemm as the matrix expressions of ORBmatcher.cc:1304-1312,:1325 use it: A*B+C (flags 0) and -A.t()*B (GEMM_1_T)
+    T = (rng.normal(size=(400, 4, 4)) * rng.choice([0.01, 1, 10, 100], (400, 1, 1))).astype(np.float32)
+    X = (rng.normal(size=(400, 3, 1)) * rng.choice([0.1, 1, 50], (400, 1, 1))).astype(np.float32)
+    d["gemm_T"] = T; d["gemm_x"] = X
+    d["gemm_abc"] = np.stack([cv2.gemm(np.ascontiguousarray(t[:3, :3]), x, 1.0, np.ascontiguousarray(t[:3, 3:4]), 1.0) for t, x in zip(T, X)])
+    d["gemm_at_b"] = np.stack([cv2.gemm(np.ascontiguousarray(t[:3, :3]), np.ascontiguousarray(t[:3, 3:4]), -1.0, None, 0.0, flags=cv2.GEMM_1_T) for t in T])
     np.savez_compressed(os.path.join(OUT, "primitives.npz"), **d)
 
 
@@ -65,7 +75,39 @@ def extraction():
         print(name, len(kp), "glibc build:", len(kg), "differs by", len(sg - sc), "/", len(sc - sg))
 
 
+def case_digest(c):
+    import hashlib
+    h = hashlib.sha256()
+    for k in sorted(c):
+        if isinstance(c[k], np.ndarray):
+            h.update(k.encode()); h.update(str(c[k].dtype).encode()); h.update(np.ascontiguousarray(c[k]).tobytes())
+        else:
+            h.update(("%s=%r" % (k, c[k])).encode())
+    return h.hexdigest()
+
+
+GOLDEN_SEEDS = {"init": [0, 1, 2, 5, 7, 9], "proj_frame": [0, 1, 2, 3, 5, 7], "proj_points": [0, 1, 2, 3, 4, 5], "area": [0, 1, 2, 3],
+                "distinct": [0, 1, 5], "undistort": [0, 1, 2, 3, 4], "bounds": [0, 1, 2, 3, 4], "maxima": list(range(12)), "distance": [0]}
+
+
+def matcher():
+    from oracle import matcher_cases as mc
+    for kind, seeds in GOLDEN_SEEDS.items():
+        d = {"seeds": np.array(seeds, np.int32)}
+        for s in seeds:
+            c = mc.make_case(kind, s)
+            d["digest_%d" % s] = np.array(case_digest(c))
+            for k, v in mc.run_reference(kind, c).items():
+                d["%s_%d" % (k, s)] = v
+        np.savez_compressed(os.path.join(OUT, "matcher_%s.npz" % kind), **d)
+        print("matcher_%s.npz: %d cases" % (kind, len(seeds)))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if len(sys.argv) > 1 and sys.argv[1] == "matcher":
+        matcher()
+        sys.exit(0)
     primitives()
     extraction()
+    matcher()
