@@ -192,6 +192,18 @@ int os1_undistort_keypoints(const os1_keypoint* kp, int n, const float* K4, cons
 /* Frame::ComputeImageBounds (src/Frame.cc:322-353): bounds4 = {mnMinX, mnMaxX, mnMinY, mnMaxY}. */
 int os1_image_bounds(int cols, int rows, const float* K4, const float* dist, int ndist, int mode, float* bounds4, int device);
 
+/* ---- wire records of os1's map files (host memory; no GPU work) ------------------------------------------------------
+ * Osmap::serialize / deserialize of a descriptor (src/Osmap.cpp:775-786): every 1 x 32 CV_8U row is stored as eight 32-bit
+ * blocks, `((unsigned int*)m.data)[i]` — the host's byte order.  desc: n x 32 bytes (the matrix os1_orb_extract returns),
+ * blocks: n x 8.  DBoW2's per-descriptor rows (Converter::toDescriptorVector, src/Converter.cc:27-36) are the matrix rows
+ * themselves and need no call. */
+int os1_osmap_descriptor_blocks(const uint8_t* desc, int n, uint32_t* blocks);
+int os1_osmap_descriptors_from_blocks(const uint32_t* blocks, int n, uint8_t* desc);
+/* Osmap::serialize / deserialize of a keypoint (src/Osmap.cpp:819-831): the record keeps pt.x, pt.y, octave and angle; a keypoint
+ * read back has size 0, response 0 and class_id -1 (cv::KeyPoint's defaults; angle and octave as stored). */
+int os1_osmap_keypoint_records(const os1_keypoint* kp, int n, float* ptx, float* pty, int32_t* octave, float* angle);
+int os1_osmap_keypoints_from_records(const float* ptx, const float* pty, const int32_t* octave, const float* angle, int n, os1_keypoint* kp);
+
 /* os1_hamming_knn2 for callers that must not allocate.  This entry point has no counterpart in the reference
  * (os1 has no GPU code and so no allocation policy to mirror); it exists for the hosts this library gets embedded in.
  *
@@ -199,10 +211,11 @@ int os1_image_bounds(int cols, int rows, const float* K4, const float* dist, int
  * cudaMallocAsync) can take the driver's allocator lock or synchronise the device at an unpredictable moment; a
  * process whose device memory was divided up front between components, where a late allocation may simply fail;
  * a plug-in running inside a host application that forbids allocation on its worker threads.  os1_hamming_knn2
- * obtains its per-call scratch from the stream-ordered allocator and is therefore not suitable for them.
+ * takes its scratch from a pool that grows with cudaMalloc whenever a problem is larger than any before it, or when a
+ * call overlaps one on another stream, and is therefore not suitable for them.
  *
- * What it does differently: the scratch (one 8-byte partial result per row of A and per partition of B) is a fixed
- * 1 MiB array inside the library's device image.  It is present on every GPU that loads the library, from load until
+ * What it does differently: the scratch (one 8-byte partial result per row of A and per partition of B, plus 64 merge
+ * tickets) is a fixed 1 MiB array inside the library's device image.  It is present on every GPU that loads the library, from load until
  * the process exits.  The call performs no cudaMalloc, cudaFree, cudaMallocAsync or any other allocating call.
  * A, B and the three outputs are DEVICE pointers on `device`, supplied by the caller; results are identical to
  * os1_hamming_knn2 with on_device = 1.  The work is enqueued on cuda_stream (may be NULL) and not waited for.
@@ -210,8 +223,9 @@ int os1_image_bounds(int cols, int rows, const float* K4, const float* dist, int
  * Limits: nA <= 4096 and nB <= 65536; anything larger returns OS1_E_CAPACITY and launches nothing.
  * First use: the first call on a given device looks up the device address of the built-in array (a one-time
  * runtime query, made with that device current).  Make that first call during start-up, before any stream capture.
- * Sharing: all calls on one GPU use the same array, and it keeps whatever the previous call left in it.  Nothing needs
- * clearing between calls (each call overwrites every entry it later reads), but two calls whose kernels can overlap on
+ * Sharing: all calls on one GPU use the same array, and it keeps whatever the previous call left in it.  The partial
+ * results need no clearing between calls (each call overwrites every entry it later reads); the merge tickets must be
+ * zero when a call starts, and every call leaves them at zero when its kernel ends.  Two calls whose kernels can overlap on
  * the same GPU — different streams, or different host threads — race on it and return garbage: serialise them. */
 int os1_hamming_knn2_noalloc(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t* best_idx, int32_t* best_dist,
                              int32_t* second_dist, int device, void* cuda_stream);

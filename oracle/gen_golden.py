@@ -87,7 +87,7 @@ def case_digest(c):
 
 
 GOLDEN_SEEDS = {"init": [0, 1, 2, 5, 7, 9], "proj_frame": [0, 1, 2, 3, 5, 7], "proj_points": [0, 1, 2, 3, 4, 5], "area": [0, 1, 2, 3],
-                "distinct": [0, 1, 5], "undistort": [0, 1, 2, 3, 4], "bounds": [0, 1, 2, 3, 4], "maxima": list(range(12)), "distance": [0]}
+                "distinct": [0, 1, 5], "undistort": [0, 1, 2, 3, 4], "bounds": [0, 1, 2, 3, 4], "maxima": list(range(12)), "distance": [0], "wire": [0, 1]}
 
 
 def matcher():

@@ -11,7 +11,7 @@ import numpy as np
 
 from oracle import pyoracle as po
 
-KINDS = ("init", "proj_frame", "proj_points", "area", "distinct", "undistort", "bounds", "maxima", "distance")
+KINDS = ("init", "proj_frame", "proj_points", "area", "distinct", "undistort", "bounds", "maxima", "distance", "wire")
 SCALE = np.array([1.0, 1.2000000477, 1.4400000572, 1.7280001640, 2.0736002922, 2.4883203506, 2.9859845638, 3.5831816196], np.float32)
 
 
@@ -146,6 +146,11 @@ def make_case(kind, seed):
         A = rng.integers(0, 256, (400, 32), dtype=np.uint8); B = rng.integers(0, 256, (400, 32), dtype=np.uint8)
         B[:50] = A[:50]; A[:8] = [[0] * 32, [255] * 32] * 4; B[:4] = 0; B[4:8] = 255
         c.update(A=A, B=B)
+    elif kind == "wire":
+        n = 300
+        desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        desc[0] = 0; desc[1] = 255; desc[2] = np.arange(32)
+        c.update(desc=desc, kp=_keypoints(rng, n, w, h))
     else:
         raise ValueError(kind)
     return c
@@ -179,6 +184,10 @@ def run_reference(kind, c):
         return {"ind": np.array(R.three_maxima(c["sizes"]), np.int32)}
     if kind == "distance":
         return {"d": np.array([R.descriptor_distance(a, b) for a, b in zip(c["A"], c["B"])], np.int32)}
+    if kind == "wire":
+        blocks, back = R.osmap_descriptor(c["desc"])
+        xya, octv = R.osmap_keypoints(c["kp"])
+        return {"blocks": blocks, "back": back, "xya": xya, "octave": octv}
     raise ValueError(kind)
 
 
@@ -219,6 +228,11 @@ def run_oracle(kind, c):
     if kind == "distance":
         L = O.lib()
         return {"d": np.array([L.orc_descriptor_distance(po._p(np.ascontiguousarray(a)), po._p(np.ascontiguousarray(b))) for a, b in zip(c["A"], c["B"])], np.int32)}
+    if kind == "wire":
+        # Osmap.cpp:775-786, :819-831 restated: rows re-read as eight native 32-bit words; the record keeps x, y, octave, angle
+        d = np.ascontiguousarray(c["desc"])
+        return {"blocks": d.view(np.uint32).reshape(-1, 8).copy(), "back": d.copy(), "xya": np.ascontiguousarray(c["kp"][:, :3]),
+                "octave": c["kp"][:, 3].astype(np.int32)}
     raise ValueError(kind)
 
 

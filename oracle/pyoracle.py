@@ -465,6 +465,8 @@ class RefMatch:
             L.rm_undistort.argtypes = [_vp, _i, _vp, _vp, _i, _i, _vp]
             L.rm_image_bounds.argtypes = [_i, _i, _vp, _vp, _i, _i, _vp]
             L.rm_distinctive_descriptors.argtypes = [_vp, _vp, _vp, _i, _vp, _vp]
+            L.rm_osmap_descriptor_blocks.argtypes = [_vp, _i, _vp, _vp]
+            L.rm_osmap_keypoints.argtypes = [_vp, _i, _vp, _vp]
             cls._lib = L
         return cls._lib
 
@@ -562,3 +564,19 @@ class RefMatch:
         out = np.zeros((max(m, 1), 32), np.uint8); valid = np.zeros(max(m, 1), np.uint8)
         cls.lib().rm_distinctive_descriptors(_p(desc), _p(ptr), None if bad is None else _p(bad), m, _p(out), _p(valid))
         return out[:m], valid[:m].astype(bool)
+
+    @classmethod
+    def osmap_descriptor(cls, desc):
+        """Osmap::serialize + deserialize of every row (Osmap.cpp:775-786): (blocks n x 8 uint32, rows read back)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        blocks = np.zeros((len(desc), 8), np.uint32); back = np.zeros_like(desc)
+        cls.lib().rm_osmap_descriptor_blocks(_p(desc), len(desc), _p(blocks), _p(back))
+        return blocks, back
+
+    @classmethod
+    def osmap_keypoints(cls, kp):
+        """Osmap::serialize + deserialize of every keypoint (Osmap.cpp:819-831): (n x {x, y, angle}, octave)."""
+        kp = cls._kp(kp)
+        xya = np.zeros((len(kp), 3), np.float32); octv = np.zeros(len(kp), np.int32)
+        cls.lib().rm_osmap_keypoints(_p(kp), len(kp), _p(xya), _p(octv))
+        return xya, octv

@@ -6,6 +6,7 @@
 //   Frame::AssignFeaturesToGrid / GetFeaturesInArea / PosInGrid / UndistortKeyPoints / ComputeImageBounds /
 //   antidistorsionarProyeccionEquidistante         /root/reference/src/Frame.cc:114-129, :209-274, :286-384
 //   MapPoint::ComputeDistinctiveDescriptors        /root/reference/src/MapPoint.cc:227-292
+//   Osmap::serialize / deserialize of a descriptor and of a keypoint    /root/reference/src/Osmap.cpp:775-787, :819-831
 // The bodies are cut out of the reference tree by path and line range when this file is built (oracle/slice_reference.py
 // -> oracle/_ref/gen_*.inc, git-ignored) and compiled between the stub declarations of stubs.hpp.  Built into
 // oracle/_ref/libos1_refmatch.so; it validates the restated oracle (oracle/orb_oracle.cpp) and generates the committed
@@ -28,6 +29,8 @@ float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv;
 #include "gen_orbmatcher.inc"
 #include "gen_frame.inc"
 #include "gen_mappoint.inc"
+using namespace cv;        // Osmap.cpp:37
+#include "gen_osmap.inc"
 
 } // namespace ORB_SLAM2
 
@@ -265,6 +268,35 @@ void rm_distinctive_descriptors(const uint8_t* desc, const int* ptr, const uint8
         P.ComputeDistinctiveDescriptors();
         valid[m] = P.mDescriptor.empty() ? 0 : 1;
         if (valid[m]) memcpy(out_desc + (size_t)m * 32, P.mDescriptor.data, 32);
+    }
+}
+
+// Osmap's descriptor record: the eight 32-bit blocks of each 32-byte row (Osmap.cpp:775-779) and the row rebuilt from them (:781-786)
+void rm_osmap_descriptor_blocks(const uint8_t* desc, int n, unsigned int* blocks, uint8_t* back)
+{
+    Osmap om;
+    for (int i = 0; i < n; i++) {
+        cv::Mat row(1, 32, CV_8U, (void*)(desc + (size_t)i * 32));
+        SerializedDescriptor sd;
+        om.serialize(row, &sd);
+        for (int k = 0; k < 8; k++) blocks[8 * i + k] = sd.block(k);
+        cv::Mat m;
+        om.deserialize(sd, m);
+        memcpy(back + (size_t)i * 32, m.data, 32);
+    }
+}
+// Osmap's keypoint record (Osmap.cpp:819-831): rows in = x, y, angle, octave; rec = ptx, pty, octave, angle as stored
+void rm_osmap_keypoints(const float* kp, int n, float* rec_xy_angle, int* rec_octave)
+{
+    Osmap om;
+    std::vector<cv::KeyPoint> v;
+    fill_keys(v, kp, n);
+    for (int i = 0; i < n; i++) {
+        SerializedKeypoint sk;
+        om.serialize(v[i], &sk);
+        cv::KeyPoint k2;
+        om.deserialize(sk, k2);
+        rec_xy_angle[3 * i] = k2.pt.x; rec_xy_angle[3 * i + 1] = k2.pt.y; rec_xy_angle[3 * i + 2] = k2.angle; rec_octave[i] = k2.octave;
     }
 }
 

@@ -86,4 +86,32 @@ public:
     bool mbCheckOrientation;
 };
 
+// Osmap's wire records (protobuf messages in the reference, osmap.proto): only the accessors Osmap.cpp:775-787, :819-831 call
+class SerializedDescriptor {
+public:
+    std::vector<unsigned int> blocks;
+    void add_block(unsigned int v) { blocks.push_back(v); }
+    unsigned int block(int i) const { return blocks[i]; }
+    int block_size() const { return (int)blocks.size(); }
+};
+class SerializedKeypoint {
+public:
+    float x = 0, y = 0, a = 0; int o = 0;
+    void set_ptx(float v) { x = v; }
+    void set_pty(float v) { y = v; }
+    void set_octave(int v) { o = v; }
+    void set_angle(float v) { a = v; }
+    float ptx() const { return x; }
+    float pty() const { return y; }
+    int octave() const { return o; }
+    float angle() const { return a; }
+};
+class Osmap {
+public:
+    void serialize(const cv::Mat& m, SerializedDescriptor* serializedDescriptor);
+    void deserialize(const SerializedDescriptor& serializedDescriptor, cv::Mat& m);
+    void serialize(const cv::KeyPoint& kp, SerializedKeypoint* serializedKeypoint);
+    void deserialize(const SerializedKeypoint& serializedKeypoint, cv::KeyPoint& kp);
+};
+
 } // namespace ORB_SLAM2

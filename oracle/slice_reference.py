@@ -38,6 +38,12 @@ SLICES = {
     "gen_mappoint.inc": ("src/MapPoint.cc", [
         (227, 292, "void MapPoint::ComputeDistinctiveDescriptors()", "}"),
     ]),
+    "gen_osmap.inc": ("src/Osmap.cpp", [
+        (775, 779, "void Osmap::serialize(const Mat &m, SerializedDescriptor", "}"),
+        (781, 786, "void Osmap::deserialize(const SerializedDescriptor", "}"),
+        (819, 824, "void Osmap::serialize(const KeyPoint &kp, SerializedKeypoint", "}"),
+        (826, 831, "void Osmap::deserialize(const SerializedKeypoint", "}"),
+    ]),
 }
 
 

@@ -45,6 +45,10 @@ SYMBOLS = [
     ("os1_image_bounds", _i, [_i, _i, _vp, _vp, _i, _i, _vp, _i]),
     ("os1_hamming_window", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     ("os1_distinctive_descriptors", _i, [_vp, _vp, _i, _vp, _vp, _i, _i, _vp]),
+    ("os1_osmap_descriptor_blocks", _i, [_vp, _i, _vp]),
+    ("os1_osmap_descriptors_from_blocks", _i, [_vp, _i, _vp]),
+    ("os1_osmap_keypoint_records", _i, [_vp, _i, _vp, _vp, _vp, _vp]),
+    ("os1_osmap_keypoints_from_records", _i, [_vp, _vp, _vp, _vp, _i, _vp]),
 ]
 
 _lib = None

@@ -869,6 +869,57 @@ static int sm_count(int device)
     return cache[device];
 }
 
+// ---- scratch pool of os1_hamming_knn2 ----------------------------------------------------------------------------------
+// A workspace is reused at once by a call on the stream that used it last (stream order keeps the two launches apart) and by
+// any other stream once its last launch has finished; otherwise another workspace is made.  Tickets are zeroed when a
+// workspace is created and are handed back at zero by every launch.
+namespace {
+struct HammingWs {
+    int device = -1;
+    uint2* partials = nullptr; size_t nPartials = 0;
+    unsigned* tickets = nullptr; int nTickets = 0;
+    cudaEvent_t done = nullptr;
+    cudaStream_t lastStream = nullptr;
+    bool used = false;
+};
+std::mutex g_hwsMu;
+std::vector<HammingWs*> g_hws;
+
+cudaError_t hws_acquire(int device, cudaStream_t s, size_t nPartials, int nTickets, HammingWs** out)
+{
+    HammingWs* ws = nullptr;
+    for (HammingWs* w : g_hws) {
+        if (w->device != device) continue;
+        if (!w->used || w->lastStream == s || cudaEventQuery(w->done) == cudaSuccess) { ws = w; break; }
+        cudaGetLastError();       // (cudaErrorNotReady is not an error)
+    }
+    if (!ws) {
+        ws = new HammingWs();
+        ws->device = device;
+        cudaError_t e = cudaEventCreateWithFlags(&ws->done, cudaEventDisableTiming);
+        if (e != cudaSuccess) { delete ws; return e; }
+        g_hws.push_back(ws);
+    }
+    if (ws->nPartials < nPartials || ws->nTickets < nTickets) {
+        if (ws->used) { cudaError_t e = cudaEventSynchronize(ws->done); if (e != cudaSuccess) return e; }
+        const size_t np = std::max(nPartials, (size_t)64 * 1024);
+        const int nt = std::max(nTickets, 256);
+        if (ws->partials) cudaFree(ws->partials);
+        if (ws->tickets) cudaFree(ws->tickets);
+        ws->partials = nullptr; ws->tickets = nullptr; ws->nPartials = 0; ws->nTickets = 0;
+        cudaError_t e = cudaMalloc((void**)&ws->partials, np * sizeof(uint2));
+        if (e == cudaSuccess) e = cudaMalloc((void**)&ws->tickets, (size_t)nt * sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaMemset(ws->tickets, 0, (size_t)nt * sizeof(unsigned));
+        if (e == cudaSuccess) e = cudaStreamSynchronize(0);
+        if (e != cudaSuccess) return e;
+        ws->nPartials = np; ws->nTickets = nt;
+    }
+    ws->used = true; ws->lastStream = s;
+    *out = ws;
+    return cudaSuccess;
+}
+} // namespace
+
 int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t* best_idx, int32_t* best_dist, int32_t* second_dist,
                      int on_device, int device, void* cuda_stream)
 {
@@ -879,29 +930,31 @@ int os1_hamming_knn2(const uint8_t* A, int nA, const uint8_t* B, int nB, int32_t
     DeviceScope _ds(device); CK(_ds.err, "cudaSetDevice (no CPU fallback)");
     cudaStream_t s = (cudaStream_t)cuda_stream;
     const int nSplit = os1_hamming_splits(nA, nB, sm_count(device));
-    uint64_t* scratch = nullptr;
-    CK(cudaMallocAsync((void**)&scratch, (size_t)nSplit * nA * 8, s), "cudaMallocAsync(hamming partials)");
-    int rc = OS1_OK;
+    // scratch (per-split partials + merge tickets) comes from a small per-process pool: a steady-state call allocates nothing
+    std::lock_guard<std::mutex> lk(g_hwsMu);
+    HammingWs* ws = nullptr;
+    cudaError_t e = hws_acquire(device, s, (size_t)nSplit * nA, os1_hamming_row_blocks(nA), &ws);
+    if (e != cudaSuccess) return cuda_fail(nullptr, e, "os1_hamming_knn2: workspace");
     if (on_device) {
-        cudaError_t e = os1_launch_hamming_knn2_splits(A, nA, B, nB, best_idx, best_dist, second_dist, scratch, nSplit, s);
-        cudaFreeAsync(scratch, s);
+        e = os1_launch_hamming_knn2_splits(A, nA, B, nB, best_idx, best_dist, second_dist, (uint64_t*)ws->partials, nSplit, s, ws->tickets);
+        if (e == cudaSuccess) e = cudaEventRecord(ws->done, s);
         if (e != cudaSuccess) return cuda_fail(nullptr, e, "hamming kernel");
-        return rc;
+        return OS1_OK;
     }
     uint8_t *dA = nullptr, *dB = nullptr; int* dOut = nullptr;
-    cudaError_t e = cudaMallocAsync((void**)&dA, (size_t)nA * 32, s);
+    e = cudaMallocAsync((void**)&dA, (size_t)nA * 32, s);
     if (e == cudaSuccess) e = cudaMallocAsync((void**)&dB, (size_t)std::max(nB, 1) * 32, s);
     if (e == cudaSuccess) e = cudaMallocAsync((void**)&dOut, (size_t)nA * 12, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(dA, A, (size_t)nA * 32, cudaMemcpyHostToDevice, s);
     if (e == cudaSuccess && nB > 0) e = cudaMemcpyAsync(dB, B, (size_t)nB * 32, cudaMemcpyHostToDevice, s);
-    if (e == cudaSuccess) e = os1_launch_hamming_knn2_splits(dA, nA, dB, nB, dOut, dOut + nA, dOut + 2 * nA, scratch, nSplit, s);
+    if (e == cudaSuccess) e = os1_launch_hamming_knn2_splits(dA, nA, dB, nB, dOut, dOut + nA, dOut + 2 * nA, (uint64_t*)ws->partials, nSplit, s, ws->tickets);
+    if (e == cudaSuccess) e = cudaEventRecord(ws->done, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(best_idx, dOut, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(best_dist, dOut + nA, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaMemcpyAsync(second_dist, dOut + 2 * nA, (size_t)nA * 4, cudaMemcpyDeviceToHost, s);
     if (dA) cudaFreeAsync(dA, s);
     if (dB) cudaFreeAsync(dB, s);
     if (dOut) cudaFreeAsync(dOut, s);
-    cudaFreeAsync(scratch, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) return cuda_fail(nullptr, e, "os1_hamming_knn2");
     return OS1_OK;

@@ -13,6 +13,7 @@
 // problem fills the GPU; the per-split partials go through a scratch array and a small merge kernel.
 // window (CSR candidate lists, what Frame::GetFeaturesInArea returns, src/Frame.cc:209-262): one warp per row.
 #include "os1_internal.cuh"
+#include "hamming_dist.cuh"
 #include "../../include/os1_b200.h"
 #include <climits>
 #include <mutex>
@@ -25,31 +26,33 @@
 
 namespace {
 
-// 256-bit Hamming distance.  POPC issues at a quarter of the LOP3 rate, so the eight XOR words are first squeezed
-// through four carry-save adders (sum = a^b^c, carry = majority: one LOP3 each) into two weight-1 words, one weight-2
-// word and one weight-4 word: 4 POPC instead of 8 (48-frame sweep: 539 -> 760 G descriptor pairs/s on a B200).
-__device__ __forceinline__ void csa(unsigned a, unsigned b, unsigned c, unsigned& sum, unsigned& carry)
+__device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1) { return os1_dist256(a0, a1, b0, b1); }
+
+// merge of the per-split partials of one row (ascending index ranges: the earlier split wins ties)
+__device__ __forceinline__ void merge_row(const uint2* partial, int row, int nA, int nSplit, int splitLen, int* bestIdx, int* bestDist, int* secondDist)
 {
-    sum = a ^ b ^ c;
-    carry = (a & b) | (c & (a ^ b));
-}
-__device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
-{
-    const unsigned x0 = a0.x ^ b0.x, x1 = a0.y ^ b0.y, x2 = a0.z ^ b0.z, x3 = a0.w ^ b0.w;
-    const unsigned x4 = a1.x ^ b1.x, x5 = a1.y ^ b1.y, x6 = a1.z ^ b1.z, x7 = a1.w ^ b1.w;
-    unsigned sa, ca, sb, cb, sc, cc, sd, cd;
-    csa(x0, x1, x2, sa, ca);
-    csa(x3, x4, x5, sb, cb);
-    csa(x6, x7, sa, sc, cc);
-    csa(ca, cb, cc, sd, cd);
-    return __popc(sb) + __popc(sc) + 2 * __popc(sd) + 4 * __popc(cd);
+    int bd = INT_MAX, bi = -1, sd = INT_MAX;
+    for (int s = 0; s < nSplit; s++) {
+        const uint2 p = __ldcg(partial + (long long)s * nA + row);       // written by other CTAs of this launch: read through L2
+        if (p.x == HM_EMPTY) continue;
+        const int d = (int)(p.x >> HM_POSBITS), i = s * splitLen + (int)(p.x & HM_POSMASK);
+        const int d2 = p.y == HM_EMPTY ? INT_MAX : (int)(p.y >> HM_POSBITS);
+        if (d < bd) { sd = min(bd, d2); bd = d; bi = i; }
+        else sd = min(sd, d);
+    }
+    bestIdx[row] = bi; bestDist[row] = bd; secondDist[row] = sd;
 }
 
-// partial[split * nA + row] = { bestKey, secondKey } with positions relative to the split start
+// partial[split * nA + row] = { bestKey, secondKey } with positions relative to the split start.  With `counters` the
+// launch also merges: every CTA publishes its partials, then takes a ticket of its row block; the CTA that draws the last
+// ticket sees the partials of all splits (fence + atomic, the "last block" pattern), merges them and puts the counter
+// back to zero, so the counters are clean again when the launch ends — one launch instead of partial + merge.
 __global__ void __launch_bounds__(HM_ROWS) hamming_knn2_partial(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B, int nB,
-                                                                 int splitLen, uint2* __restrict__ partial)
+                                                                 int splitLen, uint2* partial, unsigned* counters, int* bestIdx,
+                                                                 int* bestDist, int* secondDist)
 {
     __shared__ uint4 tile[HM_TILE * 2];
+    __shared__ unsigned ticket;
     const int row = blockIdx.x * HM_ROWS + threadIdx.x;
     const int jb = blockIdx.y * splitLen, je = min(nB, jb + splitLen);
     uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
@@ -68,7 +71,24 @@ __global__ void __launch_bounds__(HM_ROWS) hamming_knn2_partial(const uint4* __r
             best = min(best, k);
         }
     }
+    if (counters && gridDim.y == 1) {      // a single split: nothing to merge
+        if (row < nA) {
+            bestIdx[row] = best == HM_EMPTY ? -1 : (int)(best & HM_POSMASK);
+            bestDist[row] = best == HM_EMPTY ? INT_MAX : (int)(best >> HM_POSBITS);
+            secondDist[row] = second == HM_EMPTY ? INT_MAX : (int)(second >> HM_POSBITS);
+        }
+        return;
+    }
     if (row < nA) partial[(long long)blockIdx.y * nA + row] = make_uint2(best, second);
+    if (!counters) return;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) ticket = atomicAdd(counters + blockIdx.x, 1u);
+    __syncthreads();
+    if (ticket != gridDim.y - 1) return;
+    __threadfence();
+    if (row < nA) merge_row(partial, row, nA, gridDim.y, splitLen, bestIdx, bestDist, secondDist);
+    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
 }
 
 __global__ void hamming_knn2_merge(const uint2* __restrict__ partial, int nA, int nSplit, int splitLen, int* bestIdx, int* bestDist,
@@ -76,16 +96,7 @@ __global__ void hamming_knn2_merge(const uint2* __restrict__ partial, int nA, in
 {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nA) return;
-    int bd = INT_MAX, bi = -1, sd = INT_MAX;
-    for (int s = 0; s < nSplit; s++) {                      // ascending index ranges: the earlier split wins ties
-        const uint2 p = partial[(long long)s * nA + row];
-        if (p.x == HM_EMPTY) continue;
-        const int d = (int)(p.x >> HM_POSBITS), i = s * splitLen + (int)(p.x & HM_POSMASK);
-        const int d2 = p.y == HM_EMPTY ? INT_MAX : (int)(p.y >> HM_POSBITS);
-        if (d < bd) { sd = min(bd, d2); bd = d; bi = i; }
-        else sd = min(sd, d);
-    }
-    bestIdx[row] = bi; bestDist[row] = bd; secondDist[row] = sd;
+    merge_row(partial, row, nA, nSplit, splitLen, bestIdx, bestDist, secondDist);
 }
 
 __global__ void __launch_bounds__(128) hamming_window_kernel(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B,
@@ -206,6 +217,8 @@ cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, c
     return cudaGetLastError();
 }
 
+int os1_hamming_row_blocks(int nA) { return (nA + HM_ROWS - 1) / HM_ROWS; }
+
 // number of B partitions used for an nA x nB problem on a GPU with `sms` SMs
 int os1_hamming_splits(int nA, int nB, int sms)
 {
@@ -217,8 +230,10 @@ int os1_hamming_splits(int nA, int nB, int sms)
     return s;
 }
 
+// `counters` (one zero-initialised unsigned per block of HM_ROWS rows, left at zero again by the launch) selects the
+// single-launch form; without it the partials are merged by a second kernel.
 cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8_t* B, int nB, int* bestIdx, int* bestDist,
-                                           int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s)
+                                           int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s, unsigned* counters)
 {
     if (nA <= 0) return cudaSuccess;
     int splitLen = (nB + nSplit - 1) / nSplit;
@@ -226,8 +241,9 @@ cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8
     if (splitLen < HM_TILE) splitLen = HM_TILE;
     if (splitLen > (int)HM_POSMASK) return cudaErrorInvalidValue;
     dim3 grid((nA + HM_ROWS - 1) / HM_ROWS, nSplit);
-    hamming_knn2_partial<<<grid, HM_ROWS, 0, s>>>((const uint4*)A, nA, (const uint4*)B, nB, splitLen, (uint2*)scratch);
-    hamming_knn2_merge<<<(nA + 127) / 128, 128, 0, s>>>((const uint2*)scratch, nA, nSplit, splitLen, bestIdx, bestDist, secondDist);
+    hamming_knn2_partial<<<grid, HM_ROWS, 0, s>>>((const uint4*)A, nA, (const uint4*)B, nB, splitLen, (uint2*)scratch, counters, bestIdx, bestDist,
+                                                  secondDist);
+    if (!counters) hamming_knn2_merge<<<(nA + 127) / 128, 128, 0, s>>>((const uint2*)scratch, nA, nSplit, splitLen, bestIdx, bestDist, secondDist);
     return cudaGetLastError();
 }
 
@@ -242,16 +258,19 @@ cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B
 // ---- allocation-free all-pairs matcher --------------------------------------------------------------------------
 // os1_hamming_knn2_noalloc (include/os1_b200.h): same kernels as os1_hamming_knn2, but the per-split partial results
 // live in a fixed array that is part of this library's device image instead of a stream-ordered allocation.
-// Limits: nA <= 4096 rows, nB <= 65536 rows, at most 32 partitions of B -> 32 * 4096 * 8 B = 1 MiB, resident on every
-// GPU that loads the library until the process exits.
+// Limits: nA <= 4096 rows, nB <= 65536 rows, at most 32 partitions of B -> 32 * 4096 * 8 B = 1 MiB (+ 256 B of merge
+// tickets), resident on every GPU that loads the library until the process exits.
 #define OS1_NOALLOC_MAX_A 4096
 #define OS1_NOALLOC_MAX_B 65536
 #define OS1_NOALLOC_MAX_SPLITS 32
 
 static __device__ __align__(256) uint2 g_noalloc_partials[OS1_NOALLOC_MAX_SPLITS * OS1_NOALLOC_MAX_A];
+// tickets of the single-launch merge, one per block of HM_ROWS rows: zero when the library is loaded, and put back to
+// zero by every launch before it ends (the CTA that draws a row block's last ticket resets it)
+static __device__ __align__(256) unsigned g_noalloc_tickets[OS1_NOALLOC_MAX_A / HM_ROWS];
 
 namespace {
-struct NoAllocDevice { uint2* partials; int sms; bool ready; };
+struct NoAllocDevice { uint2* partials; unsigned* tickets; int sms; bool ready; };
 NoAllocDevice g_noalloc_dev[64];
 std::mutex g_noalloc_mu;
 }
@@ -287,18 +306,26 @@ extern "C" int os1_hamming_knn2_noalloc(const uint8_t* A, int nA, const uint8_t*
                 os1_internal_set_error("os1_hamming_knn2_noalloc: cudaGetSymbolAddress(scratch) failed");
                 return OS1_E_CUDA;
             }
+            unsigned* t = nullptr;
+            e = cudaGetSymbolAddress((void**)&t, g_noalloc_tickets);
+            if (e != cudaSuccess || !t) {
+                cudaGetLastError();
+                os1_internal_set_error("os1_hamming_knn2_noalloc: cudaGetSymbolAddress(tickets) failed");
+                return OS1_E_CUDA;
+            }
             int sms = 0;
             if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms <= 0) { cudaGetLastError(); sms = 148; }
-            d.partials = p; d.sms = sms; d.ready = true;
+            d.partials = p; d.tickets = t; d.sms = sms; d.ready = true;
         }
         dev = d;
     }
     int nSplit = os1_hamming_splits(nA, nB, dev.sms);
     if (nSplit > OS1_NOALLOC_MAX_SPLITS) nSplit = OS1_NOALLOC_MAX_SPLITS;
-    // Nothing in the scratch has to start at zero: the merge kernel reads exactly the nSplit x nA partials that the
-    // partial kernel of THIS call has just written; whatever an earlier call left behind is never read.
+    // The partials need no clearing: the merge reads exactly the nSplit x nA entries that THIS launch has just written, and
+    // whatever an earlier call left behind is never read.  The tickets must start at zero and do: each launch hands them
+    // back at zero.
     e = os1_launch_hamming_knn2_splits(A, nA, B, nB, best_idx, best_dist, second_dist, (uint64_t*)dev.partials, nSplit,
-                                       (cudaStream_t)cuda_stream);
+                                       (cudaStream_t)cuda_stream, dev.tickets);
     if (e != cudaSuccess) { cudaGetLastError(); os1_internal_set_error("os1_hamming_knn2_noalloc: kernel launch failed"); return OS1_E_CUDA; }
     return OS1_OK;
 }

@@ -117,8 +117,9 @@ cudaError_t os1_launch_describe(const Geometry& g, const DevPtrs& d, int nframes
                                 int* counts, cudaStream_t s);
 // Hamming: nSplit partitions of B; scratch holds nSplit * nA uint2 partials
 int os1_hamming_splits(int nA, int nB, int sms);
+int os1_hamming_row_blocks(int nA);      // merge tickets one launch needs (zero-initialised unsigned each)
 cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8_t* B, int nB, int* bestIdx, int* bestDist,
-                                           int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s);
+                                           int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s, unsigned* counters = nullptr);
 cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, int* bestIdx,
                                       int* bestDist, int* secondDist, cudaStream_t s);
 cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s);

@@ -8,7 +8,9 @@ scratch.  This file is named so that pytest collects it last: if it fails, every
 Checked here, through the C ABI, with torch only as the owner of the input/output buffers: the new entry point gives
 exactly the outputs of the existing os1_hamming_knn2 (bit-exact — integer distances and indices, the tolerance every
 Hamming test in this suite uses), on two calls in a row with different data (the second call must not see anything the
-first one left in the shared scratch), and sizes beyond the built-in scratch are refused with a clear error."""
+first one left in the shared scratch), and sizes beyond the built-in scratch are refused with a clear error.  The same
+outputs are also held against the CPU oracle's scan, and the device's free memory is read before and after a call to
+show that the call itself takes none."""
 import numpy as np
 import pytest
 
@@ -48,6 +50,29 @@ def test_noalloc_equals_existing_entry_point_twice_in_a_row():
     ref3, got3 = _run_both(A3, B3)
     for r, g in zip(ref3, got3):
         assert np.array_equal(r, g)
+
+
+def test_noalloc_agrees_with_the_oracle_and_takes_no_device_memory(oracle_lib):
+    import torch
+    from os1_b200 import matcher
+    rng = np.random.default_rng(321)
+    A = rng.integers(0, 256, (1500, 32), dtype=np.uint8); B = rng.integers(0, 256, (2600, 32), dtype=np.uint8)
+    B[40] = A[3]; B[41] = A[3]
+    dev = torch.device("cuda", 0)
+    a = torch.from_numpy(A).to(dev); b = torch.from_numpy(B).to(dev)
+    o = [torch.full((len(A),), -7, dtype=torch.int32, device=dev) for _ in range(3)]
+    s = torch.cuda.current_stream(dev).cuda_stream
+    call = lambda: matcher.hamming_knn2_noalloc_raw(a.data_ptr(), len(A), b.data_ptr(), len(B), *[t.data_ptr() for t in o], device=0, stream=s)
+    call(); torch.cuda.synchronize()                       # first use on this device: the one-time address look-up
+    free0, _ = torch.cuda.mem_get_info(dev)
+    for _ in range(3):
+        call()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(dev)
+    assert free1 == free0, "the allocation-free entry point changed the device's free memory (%d -> %d bytes)" % (free0, free1)
+    ref = oracle_lib.Oracle.hamming_knn2(A, B)
+    for r, g in zip(ref, o):
+        assert np.array_equal(r, g.cpu().numpy())
 
 
 def test_noalloc_rejects_sizes_beyond_its_scratch():
