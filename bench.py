@@ -346,7 +346,7 @@ class Bench:
             self.step_e2e()
         self.torch.cuda.synchronize(self.dev)
         s = self.reduce_max(time.perf_counter() - t0)
-        return s / steps
+        return s / steps * 1e3                 # ms per step
 
     def measure_h2d_ceiling(self, steps):
         """The same frame bytes from the same pinned buffer into the same device buffer with plain asynchronous copies and

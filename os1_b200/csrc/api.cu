@@ -149,8 +149,11 @@ cudaError_t os1_optin_smem(const void* kernel)
     for (const auto& d : done)
         if (d.first == kernel && d.second == dev) return cudaSuccess;
     int optin = 0;
+    cudaFuncAttributes fa;
     e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, kernel);
+    // (the opt-in limit covers static + dynamic shared memory together)
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
     if (e == cudaSuccess) done.push_back(std::make_pair(kernel, dev));
     return e;
 }

@@ -32,13 +32,19 @@ __device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const u
 __device__ __forceinline__ void merge_row(const uint2* partial, int row, int nA, int nSplit, int splitLen, int* bestIdx, int* bestDist, int* secondDist)
 {
     int bd = INT_MAX, bi = -1, sd = INT_MAX;
-    for (int s = 0; s < nSplit; s++) {
-        const uint2 p = __ldcg(partial + (long long)s * nA + row);       // written by other CTAs of this launch: read through L2
-        if (p.x == HM_EMPTY) continue;
-        const int d = (int)(p.x >> HM_POSBITS), i = s * splitLen + (int)(p.x & HM_POSMASK);
-        const int d2 = p.y == HM_EMPTY ? INT_MAX : (int)(p.y >> HM_POSBITS);
-        if (d < bd) { sd = min(bd, d2); bd = d; bi = i; }
-        else sd = min(sd, d);
+    for (int s0 = 0; s0 < nSplit; s0 += 8) {
+        // eight loads in flight at once (written by other CTAs of this launch: read through L2), then the ordered merge
+        uint2 p[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) p[k] = (s0 + k < nSplit) ? __ldcg(partial + (long long)(s0 + k) * nA + row) : make_uint2(HM_EMPTY, HM_EMPTY);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (p[k].x == HM_EMPTY) continue;
+            const int d = (int)(p[k].x >> HM_POSBITS), i = (s0 + k) * splitLen + (int)(p[k].x & HM_POSMASK);
+            const int d2 = p[k].y == HM_EMPTY ? INT_MAX : (int)(p[k].y >> HM_POSBITS);
+            if (d < bd) { sd = min(bd, d2); bd = d; bi = i; }
+            else sd = min(sd, d);
+        }
     }
     bestIdx[row] = bi; bestDist[row] = bd; secondDist[row] = sd;
 }

@@ -74,7 +74,11 @@ int run(int device, int iters, double* ops_per_clk_per_sm, double* ops_per_s)
     int sms = 0;
     if (cudaSetDevice(device) != cudaSuccess) return -1;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    const int blocks = sms * 8;                     // 8 x 256 threads = 64 warps per SM: full occupancy
+    int resident = 0, clockKHz = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, ubench_kernel<MODE>, 256, 0);
+    cudaDeviceGetAttribute(&clockKHz, cudaDevAttrClockRate, device);
+    if (resident < 1) resident = 1;
+    const int blocks = sms * resident;              // exactly one full wave: every SM holds `resident` blocks from start to end
     unsigned* sink = nullptr; long long* cyc = nullptr;
     if (cudaMalloc(&sink, 4) != cudaSuccess || cudaMalloc(&cyc, blocks * sizeof(long long)) != cudaSuccess) return -1;
     cudaEvent_t e0, e1;
@@ -94,8 +98,9 @@ int run(int device, int iters, double* ops_per_clk_per_sm, double* ops_per_s)
     delete[] h;
     const double per_iter = MODE == 0 ? 8.0 : (MODE == 1 ? 16.0 : 4.0);      // popc / lop3 / distances per thread per iteration
     const double thread_ops = (double)blocks * 256.0 * iters * per_iter;
-    // every SM runs its 8 resident blocks concurrently for ~`mean` cycles
-    *ops_per_clk_per_sm = 8.0 * 256.0 * iters * per_iter / mean;
+    // every SM runs its resident blocks side by side for ~`mean` SM cycles (clock64 counts at the clock the SM really runs at)
+    *ops_per_clk_per_sm = (double)resident * 256.0 * iters * per_iter / mean;
+    (void)clockKHz;
     *ops_per_s = thread_ops / (ms * 1e-3);
     cudaFree(sink); cudaFree(cyc); cudaEventDestroy(e0); cudaEventDestroy(e1);
     return 0;
