@@ -32,7 +32,7 @@ WORKLOADS = {
                 label="640x480 synthetic frames, nFeatures 1000, scale 1.2, 8 levels, FAST 20/7 (BASELINE.json configs[0])"),
     "720p": dict(rows=720, cols=1280, nfeat=1500, batch=256, config=1,
                  label="1280x720 synthetic stream, nFeatures 1500, scale 1.2, 8 levels, FAST 20/7 (BASELINE.json configs[1])"),
-    "1080p": dict(rows=1080, cols=1920, nfeat=2000, batch=128, config=2,
+    "1080p": dict(rows=1080, cols=1920, nfeat=2000, batch=256, config=2,
                   label="1920x1080 synthetic stream, nFeatures 2000, scale 1.2, 8 levels, FAST 20/7 (BASELINE.json configs[2])"),
 }
 HEADLINE = "1080p"

@@ -192,6 +192,67 @@ int os1_undistort_keypoints(const os1_keypoint* kp, int n, const float* K4, cons
 /* Frame::ComputeImageBounds (src/Frame.cc:322-353): bounds4 = {mnMinX, mnMaxX, mnMinY, mnMaxY}. */
 int os1_image_bounds(int cols, int rows, const float* K4, const float* dist, int ndist, int mode, float* bounds4, int device);
 
+/* ---- the three matching functions as WHOLE functions on the GPU ------------------------------------------------------------
+ * An os1_matcher owns every scratch buffer the calls below need (grid, candidate lists, distances, claim state); it is sized
+ * once, at creation, so a steady-state call allocates nothing.  The device entry points take DEVICE pointers — the keypoints and
+ * descriptors os1_orb_extract_batch left on the GPU, undistorted by os1_undistort_keypoints — enqueue their kernels on
+ * cuda_stream and return; results (matches and the match count) stay on the device.  Calls on one handle must be serialised
+ * (one stream, or synchronised).  If the candidate lists of a call exceed max_candidates nothing is matched, the count is 0
+ * and os1_matcher_synchronize reports OS1_E_CAPACITY.
+ * Host-side quantities that the reference keeps in static members of Frame are plain arguments here: bounds4 = {mnMinX,
+ * mnMaxX, mnMinY, mnMaxY} (Frame::ComputeImageBounds, os1_image_bounds), K4 = {fx, fy, cx, cy}. */
+typedef struct os1_matcher os1_matcher;
+#define OS1_MATCH_NONE (-1)     /* nothing attached / matched */
+#define OS1_MATCH_REMOVED (-2)  /* attached during the call, detached again by the rotation filter (the reference leaves NULL) */
+int os1_matcher_create(os1_matcher** out, int max_keypoints, int max_queries, int max_candidates, int device);
+int os1_matcher_destroy(os1_matcher* m);
+const char* os1_matcher_last_error(const os1_matcher* m);
+/* Waits for cuda_stream and reports a device-side capacity failure of the calls queued before it. */
+int os1_matcher_synchronize(os1_matcher* m, void* cuda_stream);
+
+/* int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<Point2f>& vbPrevMatched, vector<int>& vnMatches12,
+ * int windowSize)   src/ORBmatcher.cc:400-515, include/ORBmatcher.h:193 — candidate windows (GetFeaturesInArea around
+ * vbPrevMatched, level 0 only), distances, claims and steals, rotation filter when check_orientation (mbCheckOrientation),
+ * and the vbPrevMatched update (:507-510).  kp1/kp2 = mvKeysUn of the two frames, D1/D2 = mDescriptors, prev_xy = n1 x 2
+ * floats in and out, matches12 = n1 ints (index into frame 2 or -1), nmatches = one int.  nnratio = mfNNratio. */
+int os1_matcher_search_for_initialization(os1_matcher* m, const os1_keypoint* kp1, const uint8_t* D1, int n1, const os1_keypoint* kp2,
+                                          const uint8_t* D2, int n2, const float* bounds4, float* prev_xy, int window_size, float nnratio,
+                                          int check_orientation, int32_t* matches12, int32_t* nmatches, void* cuda_stream);
+/* int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th)   src/ORBmatcher.cc:1292-1423,
+ * include/ORBmatcher.h:118.  Tcw_cur = CurrentFrame.mTcw (16 floats, row major, host); per last-frame keypoint i: has_point[i]
+ * (0 = mvpMapPoints[i] is NULL, 1 = a point with observations, 2 = a point whose Observations() is 0), outlier[i] (mvbOutlier[i]), world_pos = GetWorldPos() (3 floats), D_points = GetDescriptor()
+ * (32 bytes), kp_last[i].octave / .angle.  taken[i2] (in/out, one byte per current keypoint): 0 = no map point, 1 = holds a point
+ * with observations (:1363-1365 skips it), 2 = holds a point without; a keypoint that gets a point takes that point's 1 or 2, one
+ * that loses it to the rotation filter becomes 0.  match_of_cur[i2] = index of the last-frame keypoint whose point was attached, OS1_MATCH_NONE
+ * (untouched: it keeps what it had), or OS1_MATCH_REMOVED. */
+int os1_matcher_search_by_projection_frame(os1_matcher* m, const os1_keypoint* kp_cur, const uint8_t* D_cur, int n_cur, const float* Tcw_cur,
+                                           uint8_t* taken, const os1_keypoint* kp_last, int n_last, const uint8_t* has_point,
+                                           const uint8_t* outlier, const float* world_pos, const uint8_t* D_points, const float* K4,
+                                           const float* bounds4, const float* scale_factors, int nlevels, float th, int check_orientation,
+                                           int32_t* match_of_cur, int32_t* nmatches, void* cuda_stream);
+/* int ORBmatcher::SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, const float th)   src/ORBmatcher.cc:45-124,
+ * include/ORBmatcher.h:93.  map_points: n_points x 6 floats = mTrackProjX, mTrackProjY, mTrackViewCos, mnTrackScaleLevel, flags
+ * (1 = mbTrackInView, 2 = isBad(), 4 = plCandidato), unused; D_points = GetDescriptor().  taken / match_of_frame as above
+ * (no rotation filter in this function). */
+int os1_matcher_search_by_projection_points(os1_matcher* m, const os1_keypoint* kp_frame, const uint8_t* D_frame, int n_frame, uint8_t* taken,
+                                            const float* map_points, const uint8_t* D_points, int n_points, const float* bounds4,
+                                            const float* scale_factors, int nlevels, float th, float nnratio, int32_t* match_of_frame,
+                                            int32_t* nmatches, void* cuda_stream);
+/* The same three calls with HOST buffers (used by the C++ adapter include/ORBmatcher.h): inputs are staged on the device in a
+ * buffer the handle keeps, the pipeline runs, the results are copied back and the call returns when they have arrived. */
+int os1_matcher_search_for_initialization_host(os1_matcher* m, const os1_keypoint* kp1, const uint8_t* D1, int n1, const os1_keypoint* kp2,
+                                               const uint8_t* D2, int n2, const float* bounds4, float* prev_xy, int window_size, float nnratio,
+                                               int check_orientation, int32_t* matches12, int32_t* nmatches);
+int os1_matcher_search_by_projection_frame_host(os1_matcher* m, const os1_keypoint* kp_cur, const uint8_t* D_cur, int n_cur, const float* Tcw_cur,
+                                                uint8_t* taken, const os1_keypoint* kp_last, int n_last, const uint8_t* has_point,
+                                                const uint8_t* outlier, const float* world_pos, const uint8_t* D_points, const float* K4,
+                                                const float* bounds4, const float* scale_factors, int nlevels, float th, int check_orientation,
+                                                int32_t* match_of_cur, int32_t* nmatches);
+int os1_matcher_search_by_projection_points_host(os1_matcher* m, const os1_keypoint* kp_frame, const uint8_t* D_frame, int n_frame, uint8_t* taken,
+                                                 const float* map_points, const uint8_t* D_points, int n_points, const float* bounds4,
+                                                 const float* scale_factors, int nlevels, float th, float nnratio, int32_t* match_of_frame,
+                                                 int32_t* nmatches);
+
 /* ---- wire records of os1's map files (host memory; no GPU work) ------------------------------------------------------
  * Osmap::serialize / deserialize of a descriptor (src/Osmap.cpp:775-786): every 1 x 32 CV_8U row is stored as eight 32-bit
  * blocks, `((unsigned int*)m.data)[i]` — the host's byte order.  desc: n x 32 bytes (the matrix os1_orb_extract returns),

@@ -91,7 +91,7 @@ def make_case(kind, seed):
         kpl[:, 3] = np.clip(kpl[:, 3] + rng.integers(-1, 2, nl), 0, 7)
         Dmp = _noisy_copies(rng, Dc, src, 140)
         c.update(kpc=kpc, Dc=Dc, TcwC=TcwC, taken=rng.choice([0, 0, 0, 0, 1, 2], nc).astype(np.uint8), kpl=kpl, TcwL=TcwL,
-                 has=(rng.random(nl) < 0.8).astype(np.uint8), outlier=(rng.random(nl) < 0.1).astype(np.uint8), wpos=wpos, Dmp=Dmp, K4=K4,
+                 has=((rng.random(nl) < 0.8) * np.where(rng.random(nl) < 0.1, 2, 1)).astype(np.uint8), outlier=(rng.random(nl) < 0.1).astype(np.uint8), wpos=wpos, Dmp=Dmp, K4=K4,
                  bounds=_bounds(rng, w, h), scale=SCALE, th=float(rng.choice([15, 30, 7])), check_ori=int(seed % 4 != 3))
     elif kind == "proj_points":
         nf = int(rng.integers(1, 2200)); nmp = int(rng.integers(1, 3000))

@@ -70,7 +70,7 @@ class Oracle:
             L.orc_search_for_initialization.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp]
             L.orc_undistort.argtypes = [_vp, _i, _vp, _vp, _i, _i, _vp]
             L.orc_features_in_area.argtypes = [_vp, _vp, _i, _f, _f, _f, _f, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i]
-            L.orc_search_by_projection_frame.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
+            L.orc_search_by_projection_frame.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
             L.orc_search_by_projection_points.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _f, _vp]
             L.orc_distinctive_descriptors.argtypes = [_vp, _vp, _i, _vp, _vp]
             L.orc_project_last_frame.argtypes = [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp]
@@ -232,7 +232,7 @@ class Oracle:
         return bi, bm
 
     @classmethod
-    def search_by_projection_frame(cls, Dq, Dc, ptr, cand, taken, angles_q=None, angles_c=None, touched=None):
+    def search_by_projection_frame(cls, Dq, Dc, ptr, cand, taken, angles_q=None, angles_c=None, touched=None, q_noobs=None):
         Dq = np.ascontiguousarray(Dq, np.uint8); Dc = np.ascontiguousarray(Dc, np.uint8)
         ptr = np.ascontiguousarray(ptr, np.int32); cand = np.ascontiguousarray(cand, np.int32)
         aq = None if angles_q is None else np.ascontiguousarray(angles_q, np.float32)
@@ -240,7 +240,7 @@ class Oracle:
         m = np.zeros(max(len(Dc), 1), np.int32)
         n = cls.lib().orc_search_by_projection_frame(_p(Dq), len(Dq), _p(Dc), len(Dc), _p(ptr), _p(cand), _p(taken),
                                                      None if aq is None else _p(aq), None if ac is None else _p(ac), _p(m),
-                                                     None if touched is None else _p(touched))
+                                                     None if touched is None else _p(touched), None if q_noobs is None else _p(q_noobs))
         return n, m[:len(Dc)]
 
     @classmethod
@@ -334,7 +334,8 @@ class Oracle:
         ptr, cand = cls.csr_for_queries(kpc[:, :2], kpc[:, 3].astype(np.int32), bounds, *q)
         tk = (np.asarray(taken) == 1).astype(np.uint8)                      # a point without observations does not block (:1363-1365)
         touched = np.zeros(max(len(kpc), 1), np.uint8)
-        n, m = cls.search_by_projection_frame(Dmp, Dc, ptr, cand, tk, kpl[:, 2] if check_ori else None, kpc[:, 2] if check_ori else None, touched)
+        noobs = (np.asarray(has) == 2).astype(np.uint8)
+        n, m = cls.search_by_projection_frame(Dmp, Dc, ptr, cand, tk, kpl[:, 2] if check_ori else None, kpc[:, 2] if check_ori else None, touched, noobs)
         out = m.copy()
         keep = (np.asarray(taken) != 0) & (touched[:len(kpc)] == 0)
         out[keep] = -2

@@ -159,7 +159,8 @@ int rm_search_for_initialization(const float* kp1, const uint8_t* D1, int n1, co
 
 // ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th), whole function.
 //   cur:  kpc (n x {x,y,angle,octave} undistorted), Dc, TcwC (4x4), taken[i2] = 0 none / 1 point with observations / 2 point without
-//   last: kpl (angle from mvKeysUn, octave from mvKeys: the same here), has[i] / outlier[i], world positions (3 floats) and descriptors
+//   last: kpl (angle from mvKeysUn, octave from mvKeys: the same here), has[i] (0 none, 1 point with observations, 2 point without) /
+//         outlier[i], world positions (3 floats) and descriptors
 //   K4, bounds4, scale factors.  out_match[i2] = index i of the last-frame keypoint whose point was attached, -1 none,
 //   -2 = still holds the point it came in with.
 int rm_search_by_projection_frame(const float* kpc, const uint8_t* Dc, int nc, const float* TcwC, const uint8_t* taken, const float* kpl, int nl,
@@ -181,6 +182,7 @@ int rm_search_by_projection_frame(const float* kpc, const uint8_t* Dc, int nc, c
         if (taken[i]) { pre[i].nObs = taken[i] == 1 ? 1 : 0; C.mvpMapPoints[i] = &pre[i]; }
     for (int i = 0; i < nl; i++) {
         if (!has[i]) continue;
+        pts[i].nObs = has[i] == 2 ? 0 : 1;
         pts[i].worldPos = mat_f32(3, 1, wpos + 3 * i);
         pts[i].mDescriptor = cv::Mat(1, 32, CV_8U);
         memcpy(pts[i].mDescriptor.data, Dmp + (size_t)i * 32, 32);

@@ -11,7 +11,12 @@
 #include <vector>
 #include "cvmini.hpp"
 
+#ifdef OS1_STUBS_STANDALONE          // used as plain declarations (tests/matcher_adapter_main.cpp): no sliced reference files around
+#define FRAME_GRID_ROWS 48
+#define FRAME_GRID_COLS 64
+#else
 #include "gen_frame_defs.inc"      // FRAME_GRID_ROWS / FRAME_GRID_COLS  (include/Frame.h:36-37)
+#endif
 
 namespace ORB_SLAM2 {
 

@@ -45,6 +45,16 @@ SYMBOLS = [
     ("os1_image_bounds", _i, [_i, _i, _vp, _vp, _i, _i, _vp, _i]),
     ("os1_hamming_window", _i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     ("os1_distinctive_descriptors", _i, [_vp, _vp, _i, _vp, _vp, _i, _i, _vp]),
+    ("os1_matcher_create", _i, [C.POINTER(_vp), _i, _i, _i, _i]),
+    ("os1_matcher_destroy", _i, [_vp]),
+    ("os1_matcher_last_error", C.c_char_p, [_vp]),
+    ("os1_matcher_synchronize", _i, [_vp, _vp]),
+    ("os1_matcher_search_for_initialization", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _f, _i, _vp, _vp, _vp]),
+    ("os1_matcher_search_by_projection_frame", _i, [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _i, _vp, _vp, _vp]),
+    ("os1_matcher_search_by_projection_points", _i, [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp, _vp]),
+    ("os1_matcher_search_for_initialization_host", _i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp, _i, _f, _i, _vp, _vp]),
+    ("os1_matcher_search_by_projection_frame_host", _i, [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _f, _i, _vp, _vp]),
+    ("os1_matcher_search_by_projection_points_host", _i, [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
     ("os1_osmap_descriptor_blocks", _i, [_vp, _i, _vp]),
     ("os1_osmap_descriptors_from_blocks", _i, [_vp, _i, _vp]),
     ("os1_osmap_keypoint_records", _i, [_vp, _i, _vp, _vp, _vp, _vp]),

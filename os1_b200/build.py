@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libos1_b200.so")
 UBENCH_LIB = os.path.join(HERE, "libos1_ubench.so")
-SOURCES = ["api.cu", "pyramid.cu", "fast.cu", "quadtree.cu", "describe.cu", "hamming.cu", "search.cu", "framegrid.cu", "mappoint.cu", "wire.cu"]
+SOURCES = ["api.cu", "pyramid.cu", "fast.cu", "quadtree.cu", "describe.cu", "hamming.cu", "search.cu", "framegrid.cu", "mappoint.cu", "wire.cu", "matcher_dev.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-O3"]
 

@@ -21,8 +21,6 @@
 
 namespace {
 
-struct GridGeom { float minX, minY, invW, invH; };
-
 __global__ void __launch_bounds__(FG_THREADS) grid_build_kernel(const os1_kp_dev* kp, int n, GridGeom G, int n2, int* cellStart, int* gridIdx)
 {
     extern __shared__ unsigned keys[];       // n2 (power of two >= n)
@@ -95,11 +93,13 @@ __device__ __forceinline__ int area_walk(const os1_kp_dev* kp, const int* cellSt
     return cnt;
 }
 
+// qvalid (may be NULL): queries the caller's loop skips (`continue`) have qvalid[q] == 0 and get an empty list
 __global__ void area_count_kernel(const os1_kp_dev* kp, const int* cellStart, const int* gridIdx, GridGeom G, const float* qx, const float* qy,
-                                  const float* qr, const int* qmin, const int* qmax, int nq, int* cnt)
+                                  const float* qr, const int* qmin, const int* qmax, const uint8_t* qvalid, int nq, int* cnt)
 {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
+    if (qvalid && !qvalid[q]) { cnt[q] = 0; return; }
     cnt[q] = area_walk<false>(kp, cellStart, gridIdx, G, qx[q], qy[q], qr[q], qmin ? qmin[q] : -1, qmax ? qmax[q] : -1, nullptr);
 }
 
@@ -135,35 +135,50 @@ __global__ void __launch_bounds__(FG_THREADS) area_scan_kernel(const int* cnt, i
 }
 
 __global__ void area_fill_kernel(const os1_kp_dev* kp, const int* cellStart, const int* gridIdx, GridGeom G, const float* qx, const float* qy,
-                                 const float* qr, const int* qmin, const int* qmax, int nq, const int* ptr, int* cand, int candCap)
+                                 const float* qr, const int* qmin, const int* qmax, const uint8_t* qvalid, int nq, const int* ptr, int* cand, int candCap)
 {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
+    if (qvalid && !qvalid[q]) return;
     if (ptr[q + 1] > candCap) return;        // the caller's list is too short: reported through ptr[nq] > cand_cap
     area_walk<true>(kp, cellStart, gridIdx, G, qx[q], qy[q], qr[q], qmin ? qmin[q] : -1, qmax ? qmax[q] : -1, cand + ptr[q]);
 }
 
+} // namespace
+
+// grid of a frame's keypoints: cellStart[GRID_CELLS + 1], gridIdx[n]
+cudaError_t os1_launch_grid_build(const os1_kp_dev* kp, int n, GridGeom G, int* cellStart, int* gridIdx, cudaStream_t s)
+{
+    int n2 = 1; while (n2 < n) n2 <<= 1;
+    const size_t smem = (size_t)n2 * 4;
+    if (smem > 48 * 1024) { cudaError_t e = os1_optin_smem((const void*)grid_build_kernel); if (e != cudaSuccess) return e; }
+    grid_build_kernel<<<1, FG_THREADS, smem, s>>>(kp, n, G, n2, cellStart, gridIdx);
+    return cudaGetLastError();
+}
+
+// candidate lists of nq queries against a built grid: cnt[nq] scratch, ptr[nq + 1], cand[candCap]
+cudaError_t os1_launch_area_csr(const os1_kp_dev* kp, const int* cellStart, const int* gridIdx, GridGeom G, const float* qx, const float* qy,
+                                const float* qr, const int* qmin, const int* qmax, const uint8_t* qvalid, int nq, int* cnt, int* ptr, int* cand,
+                                int candCap, cudaStream_t s)
+{
+    if (nq <= 0) return cudaMemsetAsync(ptr, 0, 4, s);
+    area_count_kernel<<<(nq + 127) / 128, 128, 0, s>>>(kp, cellStart, gridIdx, G, qx, qy, qr, qmin, qmax, qvalid, nq, cnt);
+    area_scan_kernel<<<1, FG_THREADS, 0, s>>>(cnt, nq, ptr);
+    area_fill_kernel<<<(nq + 127) / 128, 128, 0, s>>>(kp, cellStart, gridIdx, G, qx, qy, qr, qmin, qmax, qvalid, nq, ptr, cand, candCap);
+    return cudaGetLastError();
+}
+
+namespace {
+
 cudaError_t run_device(const os1_kp_dev* kp, int n, GridGeom G, const float* qx, const float* qy, const float* qr, const int* qmin, const int* qmax,
                        int nq, int* ptr, int* cand, int candCap, cudaStream_t s)
 {
-    int n2 = 1; while (n2 < n) n2 <<= 1;
     int *cellStart = nullptr, *gridIdx = nullptr, *cnt = nullptr;
     cudaError_t e = cudaMallocAsync((void**)&cellStart, (GRID_CELLS + 1) * 4, s);
     if (e == cudaSuccess) e = cudaMallocAsync((void**)&gridIdx, (size_t)std::max(n, 1) * 4, s);
     if (e == cudaSuccess) e = cudaMallocAsync((void**)&cnt, (size_t)std::max(nq, 1) * 4, s);
-    if (e == cudaSuccess) {
-        const size_t smem = (size_t)n2 * 4;
-        if (smem > 48 * 1024) e = os1_optin_smem((const void*)grid_build_kernel);
-        if (e == cudaSuccess) grid_build_kernel<<<1, FG_THREADS, smem, s>>>(kp, n, G, n2, cellStart, gridIdx);
-        if (nq > 0) {
-            area_count_kernel<<<(nq + 127) / 128, 128, 0, s>>>(kp, cellStart, gridIdx, G, qx, qy, qr, qmin, qmax, nq, cnt);
-            area_scan_kernel<<<1, FG_THREADS, 0, s>>>(cnt, nq, ptr);
-            area_fill_kernel<<<(nq + 127) / 128, 128, 0, s>>>(kp, cellStart, gridIdx, G, qx, qy, qr, qmin, qmax, nq, ptr, cand, candCap);
-        } else {
-            e = cudaMemsetAsync(ptr, 0, 4, s);
-        }
-        if (e == cudaSuccess) e = cudaGetLastError();
-    }
+    if (e == cudaSuccess) e = os1_launch_grid_build(kp, n, G, cellStart, gridIdx, s);
+    if (e == cudaSuccess) e = os1_launch_area_csr(kp, cellStart, gridIdx, G, qx, qy, qr, qmin, qmax, nullptr, nq, cnt, ptr, cand, candCap, s);
     if (cellStart) cudaFreeAsync(cellStart, s);
     if (gridIdx) cudaFreeAsync(gridIdx, s);
     if (cnt) cudaFreeAsync(cnt, s);

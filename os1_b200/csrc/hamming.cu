@@ -184,11 +184,12 @@ __global__ void __launch_bounds__(HM_ROWS) hamming_pairs_kernel(const uint4* __r
 }
 
 // dist[k] = distance(A[row of k], B[cand[k]]) for every CSR entry; one warp per row
+// (lists that end beyond `cap` entries were not written by their producer: they are left alone)
 __global__ void __launch_bounds__(128) hamming_csr_kernel(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B,
-                                                          const int* __restrict__ ptr, const int* __restrict__ cand, uint16_t* __restrict__ dist)
+                                                          const int* __restrict__ ptr, const int* __restrict__ cand, uint16_t* __restrict__ dist, int cap)
 {
     const int row = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (row >= nA) return;
+    if (row >= nA || ptr[row + 1] > cap) return;
     const uint4 a0 = __ldg(A + 2 * row), a1 = __ldg(A + 2 * row + 1);
     const int p0 = ptr[row], p1 = ptr[row + 1];
     for (int k = p0 + lane; k < p1; k += 32) {
@@ -216,10 +217,10 @@ cudaError_t os1_launch_hamming_pairs(const uint8_t* desc, const int* counts, int
     return cudaGetLastError();
 }
 
-cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s)
+cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s, int cap)
 {
     if (nA <= 0) return cudaSuccess;
-    hamming_csr_kernel<<<(nA + 3) / 4, 128, 0, s>>>((const uint4*)A, nA, (const uint4*)B, ptr, cand, dist);
+    hamming_csr_kernel<<<(nA + 3) / 4, 128, 0, s>>>((const uint4*)A, nA, (const uint4*)B, ptr, cand, dist, cap);
     return cudaGetLastError();
 }
 

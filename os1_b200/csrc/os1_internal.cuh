@@ -122,8 +122,19 @@ cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8
                                            int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s, unsigned* counters = nullptr);
 cudaError_t os1_launch_hamming_window(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, int* bestIdx,
                                       int* bestDist, int* secondDist, cudaStream_t s);
-cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s);
+cudaError_t os1_launch_hamming_csr(const uint8_t* A, int nA, const uint8_t* B, const int* ptr, const int* cand, uint16_t* dist, cudaStream_t s,
+                                   int cap = 0x7fffffff);
 void os1_internal_set_error(const char* msg);
+// Frame grid (framegrid.cu): Frame's 64 x 48 grid over the undistorted image bounds and GetFeaturesInArea on it
+#define OS1_GRID_COLS 64
+#define OS1_GRID_ROWS 48
+#define OS1_GRID_CELLS (OS1_GRID_COLS * OS1_GRID_ROWS)
+#define OS1_GRID_MAX_KP 16384
+struct GridGeom { float minX, minY, invW, invH; };
+cudaError_t os1_launch_grid_build(const os1_kp_dev* kp, int n, GridGeom G, int* cellStart, int* gridIdx, cudaStream_t s);
+cudaError_t os1_launch_area_csr(const os1_kp_dev* kp, const int* cellStart, const int* gridIdx, GridGeom G, const float* qx, const float* qy,
+                                const float* qr, const int* qmin, const int* qmax, const uint8_t* qvalid, int nq, int* cnt, int* ptr, int* cand,
+                                int candCap, cudaStream_t s);
 // Raises a kernel's dynamic shared-memory limit to the device's opt-in maximum, once per (kernel, device) and under a
 // lock, so that handles with different tile sizes — and host threads launching at the same time — never lower or race
 // on a limit another launch relies on (the attribute belongs to the function, not to a handle).

@@ -170,3 +170,87 @@ def ComputeImageBounds(cols, rows, K4, dist=None, mode=0, device=0):
     b = np.zeros(4, np.float32)
     _lib.check(_lib.load().os1_image_bounds(cols, rows, _ptr(K4), _ptr(d) if len(d) else None, len(d), mode, _ptr(b), device))
     return tuple(float(v) for v in b)
+
+
+MATCH_NONE, MATCH_REMOVED = -1, -2
+
+
+class ORBmatcher:
+    """Host-side mirror of os1's ORBmatcher for the three functions the north star names (include/ORBmatcher.h:93,:118,:193),
+    run as whole functions on the GPU through an os1_matcher handle.  Constructor arguments as in the reference
+    (`ORBmatcher(float nnratio=0.6, bool checkOri=true)`, ORBmatcher.h:71).  Frames are passed as plain arrays:
+    keypoints = structured KEYPOINT_DTYPE arrays of the UNDISTORTED keypoints, descriptors (n, 32) uint8, bounds =
+    (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+
+    TH_LOW, TH_HIGH, HISTO_LENGTH = TH_LOW, TH_HIGH, HISTO_LENGTH
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0, max_keypoints=16384, max_queries=16384, max_candidates=4 << 20):
+        self.mfNNratio = float(nnratio); self.mbCheckOrientation = bool(checkOri); self.device = device
+        self._L = _lib.load()
+        self._h = C.c_void_p()
+        _lib.check(self._L.os1_matcher_create(C.byref(self._h), max_keypoints, max_queries, max_candidates, device))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._L.os1_matcher_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != _lib.OS1_OK:
+            msg = self._L.os1_matcher_last_error(self._h)
+            raise _lib.Os1Error(rc, msg.decode() if msg else "")
+
+    @property
+    def handle(self):
+        return self._h
+
+    DescriptorDistance = staticmethod(DescriptorDistance)
+
+    def SearchForInitialization(self, kp1, D1, kp2, D2, bounds, vbPrevMatched, windowSize=10):
+        """ORBmatcher.cc:400-515.  Returns (nmatches, vnMatches12, vbPrevMatched updated)."""
+        kp1 = np.ascontiguousarray(kp1); kp2 = np.ascontiguousarray(kp2)
+        D1 = np.ascontiguousarray(D1, np.uint8).reshape(-1, 32); D2 = np.ascontiguousarray(D2, np.uint8).reshape(-1, 32)
+        b = np.ascontiguousarray(bounds, np.float32)
+        prev = np.array(vbPrevMatched, np.float32).reshape(-1, 2).copy()
+        m = np.full(max(len(kp1), 1), -1, np.int32); n = C.c_int(0)
+        self._check(self._L.os1_matcher_search_for_initialization_host(self._h, _ptr(kp1), _ptr(D1), len(kp1), _ptr(kp2), _ptr(D2), len(kp2), _ptr(b),
+                                                                       _ptr(prev), int(windowSize), self.mfNNratio, int(self.mbCheckOrientation), _ptr(m),
+                                                                       C.byref(n)))
+        return n.value, m[:len(kp1)], prev
+
+    def SearchByProjectionFrame(self, kp_cur, D_cur, Tcw_cur, taken, kp_last, has_point, outlier, world_pos, D_points, K4, bounds, scale_factors, th):
+        """SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th), ORBmatcher.cc:1292-1423.  `taken` (uint8 per current
+        keypoint: 0 none, 1 point with observations, 2 point without) is updated in place.  Returns (nmatches, match_of_cur)."""
+        kp_cur = np.ascontiguousarray(kp_cur); kp_last = np.ascontiguousarray(kp_last)
+        D_cur = np.ascontiguousarray(D_cur, np.uint8).reshape(-1, 32); D_points = np.ascontiguousarray(D_points, np.uint8).reshape(-1, 32)
+        T = np.ascontiguousarray(Tcw_cur, np.float32).reshape(16); K4 = np.ascontiguousarray(K4, np.float32); b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        has_point = np.ascontiguousarray(has_point, np.uint8); outlier = np.ascontiguousarray(outlier, np.uint8)
+        world_pos = np.ascontiguousarray(world_pos, np.float32).reshape(-1, 3)
+        assert taken.dtype == np.uint8 and taken.flags.c_contiguous and len(taken) == len(kp_cur)
+        m = np.full(max(len(kp_cur), 1), -1, np.int32); n = C.c_int(0)
+        self._check(self._L.os1_matcher_search_by_projection_frame_host(self._h, _ptr(kp_cur), _ptr(D_cur), len(kp_cur), _ptr(T), _ptr(taken), _ptr(kp_last),
+                                                                        len(kp_last), _ptr(has_point), _ptr(outlier), _ptr(world_pos), _ptr(D_points), _ptr(K4),
+                                                                        _ptr(b), _ptr(sf), len(sf), float(th), int(self.mbCheckOrientation), _ptr(m),
+                                                                        C.byref(n)))
+        return n.value, m[:len(kp_cur)]
+
+    def SearchByProjectionPoints(self, kp_frame, D_frame, taken, map_points, D_points, bounds, scale_factors, th=3):
+        """SearchByProjection(Frame& F, const vector<MapPoint*>&, th), ORBmatcher.cc:45-124.  map_points rows: mTrackProjX, mTrackProjY,
+        mTrackViewCos, mnTrackScaleLevel, flags (1 mbTrackInView, 2 isBad, 4 plCandidato), unused."""
+        kp_frame = np.ascontiguousarray(kp_frame)
+        D_frame = np.ascontiguousarray(D_frame, np.uint8).reshape(-1, 32); D_points = np.ascontiguousarray(D_points, np.uint8).reshape(-1, 32)
+        mp = np.ascontiguousarray(map_points, np.float32).reshape(-1, 6); b = np.ascontiguousarray(bounds, np.float32)
+        sf = np.ascontiguousarray(scale_factors, np.float32)
+        assert taken.dtype == np.uint8 and taken.flags.c_contiguous and len(taken) == len(kp_frame)
+        m = np.full(max(len(kp_frame), 1), -1, np.int32); n = C.c_int(0)
+        self._check(self._L.os1_matcher_search_by_projection_points_host(self._h, _ptr(kp_frame), _ptr(D_frame), len(kp_frame), _ptr(taken), _ptr(mp),
+                                                                         _ptr(D_points), len(mp), _ptr(b), _ptr(sf), len(sf), float(th), self.mfNNratio,
+                                                                         _ptr(m), C.byref(n)))
+        return n.value, m[:len(kp_frame)]
