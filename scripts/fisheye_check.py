@@ -1,3 +1,4 @@
+"""Developer check: os1_undistort_keypoints mode 1 (equidistant fisheye, Frame.cc:355-384) against the oracle (glibc tan) on 960 000 points."""
 import numpy as np, sys, os
 sys.path.insert(0, os.getcwd())
 from os1_b200 import matcher

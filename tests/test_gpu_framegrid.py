@@ -101,9 +101,10 @@ def test_undistort_identity_and_fisheye(oracle_lib, frame_kp):
     K4 = (520.0, 520.0, 640.0, 360.0)
     un = matcher.UndistortKeyPoints(k, K4, None, 1)
     ref = oracle_lib.Oracle.undistort(np.stack([k["x"], k["y"]], 1), K4, None, 1)
-    # double-precision tan() on the GPU vs glibc: results may differ in the last float bit
-    assert np.abs(un["x"] - ref[:, 0]).max() <= 1e-3 and np.abs(un["y"] - ref[:, 1]).max() <= 1e-3
-    assert ((un["x"] == ref[:, 0]) & (un["y"] == ref[:, 1])).mean() > 0.99
+    # double-precision tan() on the GPU and in glibc may differ in the last bits of the DOUBLE; the coordinates are rounded to float
+    # afterwards, so a difference could only show where a double lands within a few ulps of a float rounding boundary (about
+    # one coordinate in 10^8).  Measured: 0 of 960 000 keypoints differ (scripts/fisheye_check.py); these are asserted equal.
+    assert np.array_equal(un["x"], ref[:, 0]) and np.array_equal(un["y"], ref[:, 1])
     # the fisheye model pushes points outwards: |un - c| >= |kp - c|
     assert (np.hypot(un["x"] - 640, un["y"] - 360) >= np.hypot(k["x"] - 640, k["y"] - 360) - 1e-3).all()
 
