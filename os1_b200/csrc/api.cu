@@ -697,7 +697,9 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     static const int envChunk = getenv("OS1_CHUNK") ? std::max(1, atoi(getenv("OS1_CHUNK"))) : 0;
     static const int envRamp0 = getenv("OS1_RAMP0") ? std::max(1, atoi(getenv("OS1_RAMP0"))) : 0;
     static const int envRampPct = getenv("OS1_RAMPPCT") ? std::max(100, atoi(getenv("OS1_RAMPPCT"))) : 0;
-    const int chunk = envChunk ? envChunk : 16;
+    // chunk = about 8.5 MB of frames (28 frames at 640x480, 9 at 1280x720, 4 at 1920x1080; measured optimum at all three: small
+    // enough that little work is left when the last upload ends, large enough that the kernels of a chunk fill the GPU)
+    const int chunk = envChunk ? envChunk : std::max(2, std::min(64, (int)lround(8.5e6 / ((double)rows * cols))));
     // chunk boundaries: a geometric ramp.  The upload of chunk c+1 hides behind the kernels of chunk c only while it is
     // not longer than them, so chunks grow by less than the kernel-time / upload-time ratio per frame (1.31 at 720p over
     // PCIe 5 x16); the kernels then start after the upload of a few frames and never starve again
@@ -711,9 +713,12 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     const int nchunks = (int)cuts.size() - 1;
     if (!h->inStream) CK(cudaStreamCreateWithFlags(&h->inStream, cudaStreamNonBlocking), "cudaStreamCreate");
     if (!h->outStream) CK(cudaStreamCreateWithFlags(&h->outStream, cudaStreamNonBlocking), "cudaStreamCreate");
-    while ((int)h->chunkEv.size() < 2 * nchunks + 1) {
+    // OS1_TRACE=1: the chunk events carry timestamps and the call prints, per chunk, when its upload, its kernels and its
+    // download finished (developer aid for the pipeline's timeline; off by default)
+    static const bool trace = getenv("OS1_TRACE") && atoi(getenv("OS1_TRACE")) != 0;
+    while ((int)h->chunkEv.size() < 3 * nchunks + 2) {
         cudaEvent_t e;
-        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate");
+        CK(cudaEventCreateWithFlags(&e, trace ? cudaEventDefault : cudaEventDisableTiming), "cudaEventCreate");
         h->chunkEv.push_back(e);
     }
     // the copy streams must not run ahead of work already queued on the compute stream (buffer reuse across calls)
@@ -760,6 +765,7 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
             CKD(cudaMemcpy2DAsync(desc + (size_t)f0 * cap_per_frame * 32, (size_t)cap_per_frame * 32, dDesc + (size_t)f0 * dRow, dRow,
                                  (size_t)copyCap * 32, n, cudaMemcpyDeviceToHost, h->outStream), "download descriptors");
             CKD(cudaMemcpyAsync(counts + f0, dCnt + f0, (size_t)n * 4, cudaMemcpyDeviceToHost, h->outStream), "download counts");
+            if (trace) CKD(cudaEventRecord(h->chunkEv[2 * nchunks + 1 + c], h->outStream), "cudaEventRecord");
         }
     }
     if (alt) {       // join: everything queued on the second stream is ordered before what follows on the handle's stream
@@ -771,6 +777,17 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
     CKD(cudaMemcpyAsync(h->hostStatus, h->status.p, 4, cudaMemcpyDeviceToHost, h->stream), "download status");
     CKD(cudaStreamSynchronize(h->stream), "cudaStreamSynchronize");
     if (!out_on_device) CKD(cudaStreamSynchronize(h->outStream), "cudaStreamSynchronize");
+    if (trace && !out_on_device && !frames_on_device && !direct) {
+        fprintf(stderr, "[os1 trace] %d frames in %d chunks; ms after the call's start: chunk(frames) upload / kernels / download\n", nframes, nchunks);
+        for (int c = 0; c < nchunks; c++) {
+            float a = 0, b = 0, d = 0;
+            cudaEventElapsedTime(&a, h->chunkEv[2 * nchunks], h->chunkEv[2 * c]);
+            cudaEventElapsedTime(&b, h->chunkEv[2 * nchunks], h->chunkEv[2 * c + 1]);
+            cudaEventElapsedTime(&d, h->chunkEv[2 * nchunks], h->chunkEv[2 * nchunks + 1 + c]);
+            fprintf(stderr, "[os1 trace]  %2d(%2d) %7.3f / %7.3f / %7.3f\n", c, cuts[c + 1] - cuts[c], a, b, d);
+        }
+        cudaGetLastError();
+    }
     rc = check_status(h, h->hostStatus[0]);
     if (rc) return rc;
     if (!out_on_device)

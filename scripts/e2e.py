@@ -1,14 +1,16 @@
-"""Quick A/B of the batch paths: device-resident step and host-to-host step (256 x 720p), in ms."""
+"""Quick A/B of the batch paths: device-resident step and host-to-host step, in ms.  RES=vga|720p|1080p B=<frames> STEPS=<n>;
+the library's knobs (OS1_CHUNK, OS1_RAMP0, OS1_RAMPPCT, OS1_ALT, OS1_TRACE) are read from the environment."""
 import sys, time, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import os1_b200
 from os1_b200 import synth
-B, ROWS, COLS = int(os.environ.get("B", 256)), 720, 1280
+RES = {"vga": (480, 640, 1000), "720p": (720, 1280, 1500), "1080p": (1080, 1920, 2000)}[os.environ.get("RES", "720p")]
+B, ROWS, COLS = int(os.environ.get("B", 256)), RES[0], RES[1]
 steps = int(os.environ.get("STEPS", 30))
 dev = torch.device("cuda", 0)
 fh = torch.from_numpy(synth.video(B, ROWS, COLS, seed=1000)).pin_memory(); fd = fh.to(dev)
-ext = os1_b200.ORBextractor(1500, 1.2, 8, 20, 7, device=0)
+ext = os1_b200.ORBextractor(RES[2], 1.2, 8, 20, 7, device=0)
 cap = ext.max_keypoints(); ext.reserve(ROWS, COLS, B)
 st = torch.cuda.current_stream(dev); ext.set_stream(st.cuda_stream)
 kd = torch.empty((B, cap, 28), dtype=torch.uint8, device=dev); dd = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
