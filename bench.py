@@ -477,7 +477,29 @@ def extras(torch, os1_b200, dev):
         us = e0.elapsed_time(e1) * 1e3 / reps
         rec = {"us_per_call": us, "gpairs_per_s": pairs / us / 1e3, "gops_per_s": 24 * pairs / us / 1e3,
                "note": "1 pair = 8 XOR + 8 POPC + 8 ADD on 32-bit words (SURVEY.md 8d); device pointers"}
-        r = hroof(rec["gpairs_per_s"])
+        # the same call replayed from a CUDA graph (50 launches per graph): the GPU's own time per call, without the host's launch work
+        try:
+            gst = torch.cuda.Stream(dev)
+            gcall = lambda: matcher.hamming_knn2_noalloc_raw(a.data_ptr(), len(d0), b.data_ptr(), len(d1), o[0].data_ptr(), o[1].data_ptr(), o[2].data_ptr(),
+                                                             device=dev.index, stream=gst.cuda_stream)
+            if name == "hamming_knn2_noalloc":
+                gcall(); torch.cuda.synchronize(dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=gst):
+                    for _ in range(50):
+                        gcall()
+                g.replay(); torch.cuda.synchronize(dev)
+                e0.record(s)
+                for _ in range(10):
+                    g.replay()
+                e1.record(s); torch.cuda.synchronize(dev)
+                usg = e0.elapsed_time(e1) * 1e3 / 500
+                rec["us_per_call_gpu_only"] = usg
+                rec["gpairs_per_s_gpu_only"] = pairs / usg / 1e3
+                rec["gpu_only_note"] = "50 calls captured in a CUDA graph and replayed: no host launch work between the kernels"
+        except Exception as ex:
+            rec["us_per_call_gpu_only"] = None; rec["gpu_only_note"] = "graph replay failed: %s" % ex
+        r = hroof(rec.get("gpairs_per_s_gpu_only") or rec["gpairs_per_s"])
         if r:
             rec["roofline"] = r
         out["%s_%dx%d" % (name, len(d0), len(d1))] = rec

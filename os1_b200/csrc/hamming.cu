@@ -72,7 +72,7 @@ __global__ void __launch_bounds__(HM_ROWS) hamming_knn2_partial(const uint4* __r
         const unsigned base = (unsigned)(t0 - jb);
 #pragma unroll 4
         for (int j = 0; j < cnt; j++) {
-            const unsigned k = ((unsigned)dist256(a0, a1, tile[2 * j], tile[2 * j + 1]) << HM_POSBITS) | (base + j);
+            const unsigned k = os1_dist256_key(a0, a1, tile[2 * j], tile[2 * j + 1], base + j);
             second = min(second, max(k, best));
             best = min(best, k);
         }
@@ -103,6 +103,104 @@ __global__ void hamming_knn2_merge(const uint2* __restrict__ partial, int nA, in
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= nA) return;
     merge_row(partial, row, nA, nSplit, splitLen, bestIdx, bestDist, secondDist);
+}
+
+// All pairs for SMALL problems (a single frame pair: BASELINE config 4, 2000 x 2000) — one launch, no partials in global memory.
+// The tiled kernel above gives a thread a whole row and needs many CTAs per SM (hence a second grid dimension over B, partial
+// results and a merge) before a 2000 x 2000 problem fills the GPU.  Here the columns of B are dealt out inside the CTA instead:
+// a warp owns TWO rows of A, and its 16 lane pairs, together with one or three more warps of the same rows, split the columns 32
+// or 64 ways (column j goes to slice j mod 32 or 64).  B is staged once per CTA into shared memory by ONE bulk copy (cp.async.bulk + mbarrier: the
+// SM's copy engine streams the 64 KB of a 2000-column B while the warps fetch their rows); a warp's load then touches 16 columns,
+// each address shared by the warp's two rows, in two conflict-free wavefronts — a quarter of what one row per warp costs the
+// shared-memory pipe (that version was bound by it: l1tex 80 %, ncu).  The (best, second) keys carry global column positions, so the butterfly over a warp's slices and
+// the two-way merge across the warp pair are exact in any order.  The launcher picks the CTA height so that a problem of this size
+// is ONE CTA per SM: 2000 rows on 148 SMs -> 14 rows, 14 warps, 143 CTAs.
+#define HL_MAX_COLS 3072            // columns of B per shared-memory pass (96 KB): larger B takes several passes
+#define HL_SG_MAX 4                 // warps that can share a pair of rows
+#define HL_STAGES 4                 // bulk copies (and barriers) a pass of B is brought in with
+__global__ void __launch_bounds__(1024) hamming_knn2_lanes(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B, int nB, int cols, int SG,
+                                                           int* bestIdx, int* bestDist, int* secondDist)
+{
+    extern __shared__ __align__(128) uint4 tileB[];         // [cols][2], as in global memory
+    __shared__ __align__(8) unsigned long long bar[HL_STAGES];
+    __shared__ uint2 part[HL_SG_MAX - 1][32];               // (best, second) of the other warps of every row
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const int RG = nwarps / SG, rg = warp % RG, sg = warp / RG;
+    const int rowInCta = rg * 2 + (lane >> 4);
+    const int row = blockIdx.x * (2 * RG) + rowInCta;
+    const int slice = sg * 16 + (lane & 15);
+    // Bank layout: a warp's load touches 16 columns = 512 consecutive bytes, of which every lane wants 16.  If all lanes took the
+    // same half of their column, the 16 addresses would fall into 4 bank groups (4-way conflict); with slices 0-3 and 8-11 taking
+    // the first half first and slices 4-7 and 12-15 the second half first, every bank group is hit exactly twice: two wavefronts,
+    // the minimum for 256 bytes.  The row's halves are swapped for those lanes once, up front, so the loop does not care.
+    const int h = (lane >> 2) & 1;
+    const unsigned barAddr = (unsigned)__cvta_generic_to_shared(bar), tileAddr = (unsigned)__cvta_generic_to_shared(tileB);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < HL_STAGES; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barAddr + 8 * i));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+    if (row < nA) { a0 = __ldg(A + 2 * row + h); a1 = __ldg(A + 2 * row + (h ^ 1)); }
+    unsigned best = HM_EMPTY, second = HM_EMPTY;
+    unsigned parity = 0;
+    for (int c0 = 0; c0 < nB; c0 += cols) {
+        const int cnt = min(cols, nB - c0);
+        // the pass arrives in HL_STAGES bulk copies (the SM's copy engine streams them: no registers, no per-thread loop), each with
+        // its own barrier, so the distances of the first columns are under way while the later ones are still travelling
+        const int per = ((cnt + HL_STAGES - 1) / HL_STAGES + 63) & ~63;
+        if (c0) __syncthreads();                            // everybody is done with the previous pass's columns
+        if (threadIdx.x == 0) {
+            for (int i = 0; i < HL_STAGES; i++) {
+                const int b0 = min(i * per, cnt), b1 = min(b0 + per, cnt);
+                const unsigned bytes = (unsigned)(b1 - b0) * 32u;
+                if (bytes) {
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barAddr + 8 * i), "r"(bytes) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tileAddr + 32u * b0),
+                                 "l"(B + 2 * (long long)(c0 + b0)), "r"(bytes), "r"(barAddr + 8 * i)
+                                 : "memory");
+                } else {
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(barAddr + 8 * i) : "memory");
+                }
+            }
+        }
+#pragma unroll 1
+        for (int i = 0; i < HL_STAGES; i++) {
+            const int b0 = min(i * per, cnt), b1 = min(b0 + per, cnt);
+            unsigned done;
+            do {
+                asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(done) : "r"(barAddr + 8 * i), "r"(parity) : "memory");
+            } while (!done);
+            if (row < nA) {
+#pragma unroll 4
+                for (int j = b0 + slice; j < b1; j += 16 * SG) {   // (b0 is a multiple of 64: column j still belongs to slice j mod 16*SG)
+                    const unsigned k = os1_dist256_key(a0, a1, tileB[2 * j + h], tileB[2 * j + (h ^ 1)], (unsigned)(c0 + j));
+                    second = min(second, max(k, best));
+                    best = min(best, k);
+                }
+            }
+        }
+        parity ^= 1u;
+    }
+    // the 16 slices of this warp's two rows
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+        const unsigned ob = __shfl_xor_sync(0xffffffffu, best, o), os = __shfl_xor_sync(0xffffffffu, second, o);
+        second = min(min(second, os), max(best, ob));
+        best = min(best, ob);
+    }
+    if (sg > 0 && (lane & 15) == 0) part[sg - 1][rowInCta] = make_uint2(best, second);
+    __syncthreads();
+    if (sg == 0 && (lane & 15) == 0 && row < nA) {
+        for (int g = 0; g < SG - 1; g++) {
+            const uint2 p = part[g][rowInCta];
+            second = min(min(second, p.y), max(best, p.x));
+            best = min(best, p.x);
+        }
+        bestIdx[row] = best == HM_EMPTY ? -1 : (int)(best & HM_POSMASK);
+        bestDist[row] = best == HM_EMPTY ? INT_MAX : (int)(best >> HM_POSBITS);
+        secondDist[row] = second == HM_EMPTY ? INT_MAX : (int)(second >> HM_POSBITS);
+    }
 }
 
 __global__ void __launch_bounds__(128) hamming_window_kernel(const uint4* __restrict__ A, int nA, const uint4* __restrict__ B,
@@ -162,7 +260,7 @@ __global__ void __launch_bounds__(HM_ROWS) hamming_pairs_kernel(const uint4* __r
         __syncthreads();
 #pragma unroll 4
         for (int j = 0; j < cnt; j++) {
-            const unsigned k = ((unsigned)dist256(a0, a1, tile[2 * j], tile[2 * j + 1]) << HM_POSBITS) | (unsigned)(t0 + j);
+            const unsigned k = os1_dist256_key(a0, a1, tile[2 * j], tile[2 * j + 1], (unsigned)(t0 + j));
             second = min(second, max(k, best));
             best = min(best, k);
         }
@@ -237,12 +335,37 @@ int os1_hamming_splits(int nA, int nB, int sms)
     return s;
 }
 
+// Small problems — fewer row blocks than it takes to fill the GPU even with every split the tiled kernel could use — go to the
+// lane-split kernel: one CTA per SM, nothing to merge.  Returns false when the problem is not of that kind.
+static bool launch_lanes(const uint8_t* A, int nA, const uint8_t* B, int nB, int* bestIdx, int* bestDist, int* secondDist, int sms, cudaStream_t s,
+                         cudaError_t* err)
+{
+    if (nB < 1 || nB > (int)HM_POSMASK || nA > 16 * sms) return false;
+    int rows = (nA + sms - 1) / sms;                     // rows per CTA: one CTA per SM where that is possible
+    rows = (rows + 1) & ~1;
+    rows = rows < 4 ? 4 : (rows > 16 ? 16 : rows);
+    const int SG = 2;         // warps that share a pair of rows (4 was measured too: 9.0 instead of 8.9 us for 2000 x 2000)
+    const int warps = (rows / 2) * SG;
+    const int cols = nB < HL_MAX_COLS ? ((nB + 31) & ~31) : HL_MAX_COLS;
+    const size_t smem = (size_t)cols * 32;
+    if (smem > 48 * 1024) { *err = os1_optin_smem((const void*)hamming_knn2_lanes); if (*err != cudaSuccess) return true; }
+    hamming_knn2_lanes<<<(nA + rows - 1) / rows, warps * 32, smem, s>>>((const uint4*)A, nA, (const uint4*)B, nB, cols, SG, bestIdx, bestDist, secondDist);
+    *err = cudaGetLastError();
+    return true;
+}
+
 // `counters` (one zero-initialised unsigned per block of HM_ROWS rows, left at zero again by the launch) selects the
 // single-launch form; without it the partials are merged by a second kernel.
 cudaError_t os1_launch_hamming_knn2_splits(const uint8_t* A, int nA, const uint8_t* B, int nB, int* bestIdx, int* bestDist,
                                            int* secondDist, uint64_t* scratch, int nSplit, cudaStream_t s, unsigned* counters)
 {
     if (nA <= 0) return cudaSuccess;
+    if (counters) {
+        int dev = 0, sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaError_t e = cudaSuccess;
+        if (launch_lanes(A, nA, B, nB, bestIdx, bestDist, secondDist, sms, s, &e)) return e;
+    }
     int splitLen = (nB + nSplit - 1) / nSplit;
     splitLen = ((splitLen + HM_TILE - 1) / HM_TILE) * HM_TILE;
     if (splitLen < HM_TILE) splitLen = HM_TILE;

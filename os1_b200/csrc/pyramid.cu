@@ -83,7 +83,7 @@ __device__ __forceinline__ unsigned vresize(int h0, int h1, int b0, int b1)
 }
 
 template <bool USE_TMA>
-__global__ void __launch_bounds__(256, 5) pyramid_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PyrParams p)
+__global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ PyrParams p)
 {
     extern __shared__ __align__(128) uint8_t sm_raw[];
     // TMA wants a 128-byte aligned destination: align by hand (the launcher allocates 128 spare bytes) and keep
@@ -168,12 +168,13 @@ __global__ void __launch_bounds__(256, 5) pyramid_kernel(const __grid_constant__
                 };
                 unsigned h0[4], h1[4] = { 0, 0, 0, 0 };
                 int prev1 = -1;
+                const int4* ryp = ry + Y.x + yb;
+                uint32_t* dp = dst + yb * dpw + grp;
+                uint8_t* grow = g + (long long)(Y.x + yb) * gp + gxb;
                 // rows of the band this tile owns (the others are halo for the next level): [o0, o1)
-                const int o0 = min(max(Y.z - Y.x, yb), ye), o1 = max(min(Y.w - Y.x, ye), o0);
-                // one destination row: the two source rows through the horizontal taps (reused from the previous row where they
-                // coincide), the vertical taps, four bytes packed by permutes, one shared-memory word
-                auto row = [&](int ly) -> unsigned {
-                    const int4 ey = __ldg(ry + Y.x + ly);
+                const int o0 = max(Y.z - Y.x, yb), o1 = min(Y.w - Y.x, ye);
+                for (int ly = yb; ly < ye; ly++, ryp++, dp += dpw, grow += gp) {
+                    const int4 ey = __ldg(ryp);
                     if (ey.x == prev1) {
 #pragma unroll
                         for (int i = 0; i < 4; i++) h0[i] = h1[i];
@@ -185,34 +186,23 @@ __global__ void __launch_bounds__(256, 5) pyramid_kernel(const __grid_constant__
                     }
                     prev1 = ey.y;
                     const unsigned b0 = (unsigned)ey.z, b1 = (unsigned)ey.w;
-                    unsigned v[4];
+                    unsigned word = 0;
 #pragma unroll
-                    for (int i = 0; i < 4; i++)       // ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2, each product taken as a multiply-high
-                        v[i] = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
-                    const unsigned word = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
-                    dst[ly * dpw + grp] = word;
-                    return word;
-                };
-                // three stretches, so that the ownership test and the partial-group test leave the loop: halo above, owned rows
-                // (stored to the level in global memory: whole words for groups inside the owned columns, single bytes at the
-                // tile's left and right edge), halo below
-#pragma unroll 1
-                for (int ly = yb; ly < o0; ly++) row(ly);
-                uint8_t* grow = g + (long long)(Y.x + o0) * gp + gxb;
-                if (fullX) {
-#pragma unroll 1
-                    for (int ly = o0; ly < o1; ly++, grow += gp) *(uint32_t*)grow = row(ly);
-                } else {
-#pragma unroll 1
-                    for (int ly = o0; ly < o1; ly++, grow += gp) {
-                        const unsigned word = row(ly);
+                    for (int i = 0; i < 4; i++) {
+                        // ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2, each product taken as a multiply-high
+                        const unsigned v = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
+                        word |= v << (8 * i);
+                    }
+                    *dp = word;
+                    if (ly >= o0 && ly < o1) {
+                        if (fullX) *(uint32_t*)grow = word;
+                        else {
 #pragma unroll
-                        for (int i = 0; i < 4; i++)
-                            if (gxb + i >= X.z && gxb + i < X.w) grow[i] = (uint8_t)(word >> (8 * i));
+                            for (int i = 0; i < 4; i++)
+                                if (gxb + i >= X.z && gxb + i < X.w) grow[i] = (uint8_t)(word >> (8 * i));
+                        }
                     }
                 }
-#pragma unroll 1
-                for (int ly = o1; ly < ye; ly++) row(ly);
             }
         }
         srcX0 = gx0; srcY0 = Y.x;

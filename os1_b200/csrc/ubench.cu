@@ -52,10 +52,12 @@ __global__ void __launch_bounds__(256) ubench_kernel(unsigned seed, int iters, u
         for (int it = 0; it < iters; it += 16) {
 #pragma unroll 4
             for (int j = 0; j < 64; j++) {
-                const unsigned d = (unsigned)os1_dist256(a0, a1, tile[2 * j], tile[2 * j + 1]);
+                const unsigned d = MODE == 4 ? (unsigned)os1_dist256<1>(a0, a1, tile[2 * j], tile[2 * j + 1])
+                                   : MODE == 5 ? (unsigned)os1_dist256<2>(a0, a1, tile[2 * j], tile[2 * j + 1])
+                                               : (unsigned)os1_dist256<OS1_DIST_VARIANT>(a0, a1, tile[2 * j], tile[2 * j + 1]);
                 if (MODE == 2) sum += d;
                 else {
-                    const unsigned k = (d << 20) | (unsigned)(4 * it + j);
+                    const unsigned k = MODE == 3 ? os1_dist256_key(a0, a1, tile[2 * j], tile[2 * j + 1], (unsigned)(4 * it + j)) : ((d << 20) | (unsigned)(4 * it + j));
                     second = min(second, max(k, best));
                     best = min(best, k);
                 }
@@ -123,6 +125,7 @@ int run(int device, int iters, double* ops_per_clk_per_sm, double* ops_per_s, do
 } // namespace
 
 // out[0..1] popc, out[2..3] lop3, out[4..5] dist256, out[6..7] dist256 + best/second update: (per clock per SM, per second);
+// out[9], out[10] = scan pairs per second with distance variants 1 and 2;
 // out[8] = SM clock (MHz) while the last kernel ran (these loops keep every integer pipe busy: the chip may run them below its
 // nominal clock, which is why the per-second and per-clock figures are both given)
 extern "C" int os1_ubench_issue_rates(int device, double* out8)
@@ -134,6 +137,11 @@ extern "C" int os1_ubench_issue_rates(int device, double* out8)
     rc |= run<1>(device, 4096, out8 + 2, out8 + 3);
     rc |= run<2>(device, 2048, out8 + 4, out8 + 5);
     rc |= run<3>(device, 2048, out8 + 6, out8 + 7, out8 + 8);
+    // the same scan with fewer carry-save adders and more POPCs (hamming_dist.cuh variants 1 and 2), for the record of why
+    // the shipped variant was chosen
+    double t = 0;
+    rc |= run<4>(device, 2048, &t, out8 + 9);
+    rc |= run<5>(device, 2048, &t, out8 + 10);
     if (prev >= 0) cudaSetDevice(prev);
     return rc;
 }
