@@ -190,13 +190,21 @@ def opencv_check(w, frames):
             "fast20": tmin(lambda: [f20.detect(a) for a in lv], 2), "fast7": tmin(lambda: [f7.detect(a) for a in lv], 2)}
     ext = pyoracle.Reference(*params(w), canon=False) if pyoracle.Reference.available(canon=False) else pyoracle.Oracle(*params(w))
     whole = tmin(lambda: ext.extract(img, cap=4096), 3)
-    # the low-contrast third of the synthetic frames is where the FAST-7 retry runs (os1_b200/synth.py)
-    stage = lambda d: d["pyramid"] + d["blur"] + d["fast20"] + d["fast7"] / 3.0
+    # how many pixels the reference really hands to cv::FAST at each threshold (the per-cell windows overlap by 6 px; the retry at
+    # minThFAST runs only in cells where iniThFAST found nothing): counted by the reference build's FAST hook
+    P = float(sum(a.size for a in lv))
+    w20, w7 = 1.0, 1.0 / 3.0
+    if hasattr(ext, "fast_area"):
+        ext.extract(img, cap=4096, record=True)
+        a20, a7 = ext.fast_area()
+        w20, w7 = a20 / P, a7 / P
+    stage = lambda d: d["pyramid"] + d["blur"] + w20 * d["fast20"] + w7 * d["fast7"]
     repriced = max(whole - stage(shim) + stage(real), 1e-3)
     return {"threads": 1, "cv2": cv2.__version__, "reference_ms_per_frame": whole, "shim_stage_ms": shim, "cv2_stage_ms": real,
             "repriced_ms_per_frame": repriced, "shim_slowdown_factor": whole / repriced,
-            "note": "whole-level calls of the same primitives on the same pyramid; fast7 weighted 1/3 (the retry runs in the low-contrast "
-                    "third of the frames); repriced = reference time with its three OpenCV primitives at cv2's speed"}
+            "fast_pixels_over_level_pixels": {"iniThFAST": w20, "minThFAST_retry": w7},
+            "note": "whole-level calls of the same primitives on the same pyramid, FAST weighted by the pixels the reference really hands to "
+                    "cv::FAST at each threshold; repriced = reference time with its three OpenCV primitives at cv2's speed"}
 
 
 def cpu_baseline_sample(w, budget_s=10.0, with_opencv_check=True):

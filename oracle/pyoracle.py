@@ -387,6 +387,7 @@ class Reference:
             L.ref_candidate_count.argtypes = [_i]
             L.ref_candidates.argtypes = [_i, _vp]
             L.ref_distribute.argtypes = [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i]
+            L.ref_fast_area.argtypes = [_vp]
             cls._libs[canon] = L
         return cls._libs[canon]
 
@@ -417,6 +418,12 @@ class Reference:
         n = self.L.ref_extract(self.h, _p(img), img.shape[0], img.shape[1], img.strides[0], _p(kp), cap, _p(desc), int(record))
         assert n <= cap
         return kp[:n].copy(), desc[:n].copy()
+
+    def fast_area(self):
+        """Pixels the last extract(record=True) handed to cv::FAST at iniThFAST and at the minThFAST retry."""
+        px = np.zeros(2, np.int64)
+        self.L.ref_fast_area(_p(px))
+        return int(px[0]), int(px[1])
 
     def level_pixels(self, level, border=False):
         w, h = C.c_int(), C.c_int()

@@ -79,12 +79,17 @@ struct CandBuf {
 };
 const int MAX_LEVELS = 64;
 thread_local CandBuf g_cands[MAX_LEVELS];
+thread_local long long g_fast_px[2] = { 0, 0 };      // pixels handed to cv::FAST at the first / the retry threshold of the last recorded call
+thread_local int g_fast_th0 = -1;
 thread_local int g_cand_levels = 0;
 thread_local Probe* t_probe = nullptr;
 
-void on_fast(const cv::Mat& img, int /*threshold*/, const std::vector<cv::KeyPoint>& kps)
+void on_fast(const cv::Mat& img, int threshold, const std::vector<cv::KeyPoint>& kps)
 {
-    if (!t_probe || kps.empty()) return;
+    if (!t_probe) return;
+    if (g_fast_th0 < 0) g_fast_th0 = threshold;        // the first call of an extraction uses iniThFAST (ORBextractor.cc:848)
+    g_fast_px[threshold == g_fast_th0 ? 0 : 1] += (long long)img.rows * img.cols;
+    if (kps.empty()) return;
     for (int l = 0; l < t_probe->nlevels && l < MAX_LEVELS; l++) {
         const cv::Mat& L = t_probe->mvImagePyramid[l];
         const uint8_t* lo = L.data;
@@ -131,6 +136,7 @@ int ref_extract(void* h, const uint8_t* img, int rows, int cols, int step, float
     Probe* p = (Probe*)h;
     int n = 0;
     if (record) {
+        g_fast_px[0] = g_fast_px[1] = 0; g_fast_th0 = -1;
         for (int l = 0; l < MAX_LEVELS; l++) g_cands[l].n = 0;
         g_cand_levels = p->nlevels;
         t_probe = p;
@@ -175,6 +181,9 @@ int ref_pyramid_level(void* h, int level, uint8_t* out, int border)
         memcpy(out + (size_t)(y + b) * W, L.data + (ptrdiff_t)y * (ptrdiff_t)L.step - b, W);
     return 0;
 }
+
+// pixels the last recorded extraction handed to cv::FAST: [0] at iniThFAST (:848), [1] at the minThFAST retry (:854)
+void ref_fast_area(long long* px2) { px2[0] = g_fast_px[0]; px2[1] = g_fast_px[1]; }
 
 int ref_candidate_count(int level) { return level < g_cand_levels ? (int)g_cands[level].n : 0; }
 int ref_candidates(int level, int* xys /* n x 3 */)
