@@ -427,15 +427,24 @@ class Bench:
 
 
 def latency_record(os1_b200, w, dev):
-    """Single frame, host buffers in and out — what Frame.cc:133 sees (config 1's latency target: < 0.5 ms)."""
-    from os1_b200 import synth
+    """Single frame, host buffers in and out, through os1_orb_extract — what Frame.cc:133 sees (config 1's latency target: < 0.5 ms).
+    The image is ordinary pageable memory, as a cv::Mat is; the output buffers are allocated once, as the C++ adapter does."""
+    import ctypes as C
+    from os1_b200 import synth, _lib
+    from os1_b200.orb import KEYPOINT_DTYPE
     img = synth.frame(w["rows"], w["cols"], 0)
     e = os1_b200.ORBextractor(*params(w), device=dev.index)
+    cap = e.max_keypoints()
+    kp = np.zeros(cap, KEYPOINT_DTYPE); desc = np.zeros((cap, 32), np.uint8); n = C.c_int(0)
+    L = _lib.load()
+    call = lambda: L.os1_orb_extract(e._h, img.ctypes.data, img.shape[0], img.shape[1], img.strides[0], kp.ctypes.data, cap, desc.ctypes.data, C.byref(n))
     for _ in range(20):
-        e(img)
+        _lib.check(call(), e._h)
     ts = []
-    for _ in range(200):
-        t = time.perf_counter(); e(img); ts.append(time.perf_counter() - t)
+    for _ in range(300):
+        t = time.perf_counter(); rc = call(); ts.append(time.perf_counter() - t)
+        if rc:
+            _lib.check(rc, e._h)
     e.close()
     return float(np.median(ts) * 1e3)
 

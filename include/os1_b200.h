@@ -186,7 +186,11 @@ int os1_features_in_area(const os1_keypoint* kp, int n, float min_x, float max_x
 /* Frame::UndistortKeyPoints (src/Frame.cc:286-320).  K4 = {fx, fy, cx, cy}.  mode 0 = pinhole: cv::undistortPoints(pts, pts, K,
  * dist, Mat(), K) with dist = k1,k2,p1,p2[,k3[,k4,k5,k6[,s1..s4]]] (ndist values), the identity when dist[0] == 0 (:288-292);
  * mode 1 = os1's equidistant fisheye without distortion (antidistorsionarProyeccionEquidistante, :355-384; dist ignored).
- * kp_un receives copies of the keypoints with pt replaced (kp_un may alias kp). */
+ * kp_un receives copies of the keypoints with pt replaced (kp_un may alias kp).
+ * Parity of mode 1: the function body itself is the reference's (compiled from its source for the tests), but one product in it,
+ * `Matx33f * Vec3d` (:376), is evaluated here in double with the float matrix entries widened — which overload real OpenCV picks
+ * there cannot be checked without its headers, so that single step is an assumption (PARITY UNPINNED for it), and tan() is the
+ * device's double-precision one (0 of 960 000 test keypoints differ from glibc's after the final rounding to float). */
 int os1_undistort_keypoints(const os1_keypoint* kp, int n, const float* K4, const float* dist, int ndist, int mode, os1_keypoint* kp_un,
                             int on_device, int device, void* cuda_stream);
 /* Frame::ComputeImageBounds (src/Frame.cc:322-353): bounds4 = {mnMinX, mnMaxX, mnMinY, mnMaxY}. */
