@@ -258,6 +258,9 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
 
     // ---- 3. rounds ------------------------------------------------------------------------------------------------------
     int phase = 1, depth = 0, round = 0, buf = 0;
+    bool haveCounts = false;                      // this round's children sizes were counted by the previous round's sweep B
+    uint32_t* nextCnt = (uint32_t*)sortBuf;       // ... into the sort buffer, which is idle during a sweep
+    const int nextCap = 2 * max(P.sortCap, 2 * min(P.sortCap, 1024));      // its size in 32-bit words
     while (E > 0) {
         round++;
         uint32_t* curSize = liveSize + buf * P.maxNodes;
@@ -266,6 +269,14 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
         uint32_t* newKey = liveKey + (buf ^ 1) * P.maxNodes;
         if (depth + 1 > D) { if (tid == 0) atomicOr(P.d.status, OS1_ERR_DEPTH); break; }
         const int shift = 2 * (D - (depth + 1));
+
+        // children sizes counted by the previous round's re-labelling sweep wait in the sort buffer: move them out before the
+        // final phase sorts in it
+        if (haveCounts) {
+#pragma unroll 1
+            for (int i = tid; i < 4 * E; i += QT_THREADS) slotCnt[i] = nextCnt[i];
+            __syncthreads();
+        }
 
         // processing order: list order in a full pass (roots ascending, afterwards newest first);
         // (size, creation rank) descending in the final phase (:716-717)
@@ -288,11 +299,13 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
                 order[p] = j; procPos[j] = p;
             }
         }
+        if (!haveCounts) {
 #pragma unroll 1
         for (int i = tid; i < 4 * E; i += QT_THREADS) slotCnt[i] = 0;
         __syncthreads();
 
-        // sweep A: children sizes
+        // sweep A: children sizes (first round only: from the second round on the re-labelling sweep of the previous round has
+        // already counted them)
         // (four candidates per thread per trip: the eight loads are in flight together — the sweeps are latency bound)
 #pragma unroll 1
         for (int base = 0; base < n; base += 4 * QT_THREADS) {
@@ -313,6 +326,7 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
                     if (lane == __ffs(grp) - 1) atomicAdd(&slotCnt[slot], __popc(grp));
                 }
             }
+        }
         }
         __syncthreads();
 
@@ -394,7 +408,16 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
         }
         __syncthreads();
 
-        // sweep B: re-label candidates / vote for the best response of finished leaves
+        // sweep B: re-label candidates / vote for the best response of finished leaves — and, for the candidates that stay live,
+        // count the children of their NEW node right away (what sweep A of the next round would do with a second pass over the
+        // same candidates)
+        const bool countNext = !fin && depth + 2 <= D && 4 * newE <= nextCap;
+        const int shiftN = countNext ? shift - 2 : 0;
+        if (countNext) {
+#pragma unroll 1
+            for (int i = tid; i < 4 * newE; i += QT_THREADS) nextCnt[i] = 0;
+            __syncthreads();
+        }
 #pragma unroll 1
         for (int base = 0; base < n; base += 4 * QT_THREADS) {
             int nd[4]; uint32_t cd[4];
@@ -406,17 +429,29 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
             }
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                if (nd[u] == QT_DONE) continue;
-                const int i = base + u * QT_THREADS + tid;
-                if ((int)procPos[nd[u]] >= nSplit) {
-                    atomicMax(&leafBest[unsplitLeaf[nd[u]]], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
-                    node[i] = QT_DONE;
-                } else {
-                    const uint32_t info = slotInfo[nd[u] * 4 + ((cd[u] >> shift) & 3)];
-                    if (info & QT_LEAF) {
-                        atomicMax(&leafBest[info & 0xFFFF], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
+                int slotN = -1;
+                if (nd[u] != QT_DONE) {
+                    const int i = base + u * QT_THREADS + tid;
+                    if ((int)procPos[nd[u]] >= nSplit) {
+                        atomicMax(&leafBest[unsplitLeaf[nd[u]]], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
                         node[i] = QT_DONE;
-                    } else node[i] = (uint16_t)info;
+                    } else {
+                        const uint32_t info = slotInfo[nd[u] * 4 + ((cd[u] >> shift) & 3)];
+                        if (info & QT_LEAF) {
+                            atomicMax(&leafBest[info & 0xFFFF], (cand[i] & 0xFF000000u) | (0xFFFFFFu - i));
+                            node[i] = QT_DONE;
+                        } else {
+                            node[i] = (uint16_t)info;
+                            if (countNext) slotN = (int)info * 4 + (int)((cd[u] >> shiftN) & 3);
+                        }
+                    }
+                }
+                if (countNext) {
+                    const unsigned m = __ballot_sync(0xffffffffu, slotN >= 0);
+                    if (slotN >= 0) {
+                        const unsigned grp = __match_any_sync(m, slotN);
+                        if (lane == __ffs(grp) - 1) atomicAdd(&nextCnt[slotN], __popc(grp));
+                    }
                 }
             }
         }
@@ -424,6 +459,7 @@ __global__ void __launch_bounds__(QT_THREADS, QT_THREADS == 512 ? QT_MIN_CTAS_51
         Lcount = Lnew;
         if (fin) break;
         E = newE; phase = nextPhase; depth++; buf ^= 1;
+        haveCounts = countNext;
     }
     __syncthreads();
 
