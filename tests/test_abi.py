@@ -69,3 +69,25 @@ def test_product_never_touches_the_oracle():
                     if re.search(r"pyoracle|liboracle|orb_oracle|cv_exact|from oracle|import oracle|oracle/", txt):
                         bad.append(os.path.join(dirpath, f))
     assert not bad, bad
+
+
+def test_argument_validation_happens_before_any_cuda_call():
+    """Bad arguments are refused with OS1_E_INVALID / OS1_E_UNSUPPORTED by the entry point itself — no device needed."""
+    import ctypes as C
+    import numpy as np
+    from os1_b200 import _lib
+    L = _lib.load()
+    K4 = np.array([500, 500, 320, 240], np.float32); b = np.zeros(4, np.float32)
+    # dist == NULL with ndist > 0 (used to be dereferenced), ndist out of range, unknown mode
+    assert L.os1_image_bounds(640, 480, K4.ctypes.data, None, 4, 0, b.ctypes.data, 0) == _lib.OS1_E_INVALID
+    assert L.os1_image_bounds(640, 480, K4.ctypes.data, None, 99, 0, b.ctypes.data, 0) == _lib.OS1_E_INVALID
+    assert L.os1_image_bounds(640, 480, K4.ctypes.data, None, 0, 7, b.ctypes.data, 0) == _lib.OS1_E_INVALID
+    # the identity shortcut needs no GPU either (Frame.cc:288-292 / :345-350)
+    assert L.os1_image_bounds(640, 480, K4.ctypes.data, None, 0, 0, b.ctypes.data, 0) == _lib.OS1_OK and list(b) == [0, 640, 0, 480]
+    h = C.c_void_p()
+    assert L.os1_matcher_create(C.byref(h), 0, 10, 10, 0) == _lib.OS1_E_INVALID
+    assert L.os1_matcher_create(C.byref(h), 20000, 10, 10, 0) == _lib.OS1_E_UNSUPPORTED
+    assert L.os1_matcher_create(None, 100, 10, 10, 0) == _lib.OS1_E_INVALID
+    assert L.os1_osmap_descriptor_blocks(None, 3, None) == _lib.OS1_E_INVALID
+    assert L.os1_hamming_knn2_noalloc(None, 5000, None, 10, None, None, None, 0, None) == _lib.OS1_E_INVALID
+    assert L.os1_orb_create(C.byref(h), 1000, C.c_float(1.2), 40, 20, 7, 0) == _lib.OS1_E_UNSUPPORTED       # more than 12 levels
