@@ -397,6 +397,7 @@ class Bench:
     def record(self, steps, warmup, world, sampler=None, with_ceiling=True):
         w, B = self.w, self.B
         ms, clocks = self.measure_device(steps, warmup, sampler)
+        launches_per_step = int(self.ext.launches_per_call())            # kernels the last device-resident step launched (counted by the library)
         stage_ms = self.measure_stages()
         counts = self.cnt_d.cpu().numpy()
         e2e_ms = self.measure_e2e(steps, warmup)
@@ -430,7 +431,7 @@ class Bench:
                           "parallelism": "frame-sharded, %d rank(s), no data-path collective" % world},
                "e2e": {"value": world * B / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes,
                        "d2h_bytes_per_step": int(B * self.cap * 60 + B * 4 + 4), "ms_per_step": e2e_ms},
-               "roofline": roof}
+               "roofline": roof, "launches_per_step": launches_per_step}
         if h2d_ms:
             ceil_fps = world * B / (h2d_ms * 1e-3)
             rec["h2d_ceiling"] = {"frames_per_s": ceil_fps, "aggregate_gbs": world * h2d_bytes / (h2d_ms * 1e-3) / 1e9, "ms_per_step": h2d_ms,
@@ -694,7 +695,7 @@ def run_ours(args, rank, world, local_rank):
         return
     line = {"metric": "ORB frames/sec", "value": head["value"], "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-            "data": "synthetic", "config": head["config"], "e2e": head["e2e"], "gpu_launches": int(args.steps * 4),
+            "data": "synthetic", "config": head["config"], "e2e": head["e2e"], "gpu_launches": int(args.steps * head["launches_per_step"] * world),
             "roofline": head["roofline"], "clocks": head.get("clocks"), "h2d_ceiling": head.get("h2d_ceiling")}
     if sweep is not None:
         line["sweep"] = sweep

@@ -67,6 +67,7 @@ struct os1_orb {
     PyramidPlan* planBig = nullptr;     // larger tiles (batches)
     DevBuf rtab, ptab, gtab, slab, cellCnt, stage, cand, code, node, candCount, lvKp, lvCount, status, outKp, outDesc, outCount;
     int lastFrames = 0;
+    int lastLaunches = 4;       // kernels the last extract call launched
     const uint8_t* lastLvl0 = nullptr; long long lastLvl0Stride = 0; int lastLvl0Pitch = 0;
     // pinned host mirrors for the host-buffer path
     void* hostOut = nullptr; size_t hostOutBytes = 0;
@@ -415,9 +416,11 @@ int run_pipeline(os1_orb* h, const uint8_t* lvl0, long long lvl0Stride, int lvl0
     d.status = (int*)h->status.p;
     if (f0 == 0) { h->lastLvl0 = lvl0; h->lastLvl0Stride = lvl0Stride; h->lastLvl0Pitch = lvl0Pitch; }
     h->lastFrames = f0 + nframes;
+    PyramidPlan* const plan = (nframes >= 4 && h->planBig) ? h->planBig : h->plan;
+    h->lastLaunches = (f0 == 0 ? 0 : h->lastLaunches) + os1_pyramid_launch_count(plan, g, nframes) + 3;
     const bool t = h->timing && f0 == 0;
     if (t) CK(cudaEventRecord(h->ev[0], st), "cudaEventRecord");
-    CK(os1_launch_pyramid((nframes >= 4 && h->planBig) ? h->planBig : h->plan, g, d, nframes, st), "pyramid kernel");
+    CK(os1_launch_pyramid(plan, g, d, nframes, st), "pyramid kernel");
     if (t) CK(cudaEventRecord(h->ev[1], st), "cudaEventRecord");
     CK(os1_launch_fast(g, d, nframes, st), "FAST kernel");
     if (t) CK(cudaEventRecord(h->ev[2], st), "cudaEventRecord");
@@ -547,7 +550,7 @@ int os1_orb_set_stream(os1_orb* h, void* cuda_stream)
     return OS1_OK;
 }
 
-int os1_orb_launches_per_call(const os1_orb*) { return 4; }
+int os1_orb_launches_per_call(const os1_orb* h) { return h ? h->lastLaunches : 4; }
 
 int os1_orb_set_timing(os1_orb* h, int enable)
 {

@@ -109,6 +109,7 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH);
 void os1_pyramid_plan_destroy(PyramidPlan*);
 bool os1_pyramid_plan_ok(const PyramidPlan*);     // level-0 footprint fits a TMA box and the tile chain fits shared memory
 cudaError_t os1_launch_pyramid(PyramidPlan*, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
+int os1_pyramid_launch_count(const PyramidPlan*, const Geometry& g, int nframes);      // kernels the call above launches
 cudaError_t os1_launch_fast(const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s);
 bool os1_quadtree_fits(int maxQuota, int maxCells, int maxIni);       // the per-level state fits one CTA's shared memory
 cudaError_t os1_launch_quadtree(const Geometry& g, const DevPtrs& d, int nframes, int maxQuota, int maxCells, cudaStream_t s);

@@ -210,6 +210,116 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
     }
 }
 
+// ---- batches: one launch per level, HBM-streaming ---------------------------------------------------------------------
+// The fused chain above reads level 0 once and keeps everything else on chip, which is what a single frame wants (one launch, no
+// round trips).  For a batch the bytes were never the problem — a frame's pyramid is 10.6 MB of traffic even unfused, 1.6 us at
+// HBM speed — the instructions were: halo pixels recomputed at every level, upper levels of a tile too small for 256 threads, lanes
+// of one warp sitting in different row bands and diverging on the row-reuse logic (33 thread-instructions per output pixel).
+// Here level l is one launch over all frames: a CTA owns a 128 x PL_TH tile of the DESTINATION level, pulls the source footprint
+// of that tile in with one TMA tile load, and then a warp is a row band and a lane a group of four columns — every lane of a warp
+// walks the same rows, so the horizontally filtered source row is reused without any divergence and every output row of the tile
+// is one coalesced 128-byte store.  No pixel is computed twice; the source halo re-read is 4-5 %.
+#define PL_TW 128
+#define PL_TH 128
+struct LvlParams {
+    int level;
+    int W, H;                    // destination level
+    int boxW, boxH;              // TMA box (source footprint of a tile, inner extent a multiple of 16 bytes)
+    const int4* qtab;            // this level's QuadTaps (2 x int4 per group of four destination columns)
+    const int4* ytab;            // this level's vertical taps per destination row
+    uint8_t* dst; long long dstFrameStride; int dstPitch;
+    const uint8_t* dbgSrc; long long dbgStride; int dbgPitch, dbgW, dbgH;
+};
+
+template <bool USE_TMA>
+__global__ void __launch_bounds__(256, 6) pyramid_level_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ LvlParams p)
+{
+    extern __shared__ __align__(128) uint8_t sm_raw[];
+    uint8_t* sm = sm_raw + ((128u - ((unsigned)__cvta_generic_to_shared(sm_raw) & 127u)) & 127u);
+    __shared__ __align__(8) uint64_t bar;
+    const int lane = threadIdx.x, warp = threadIdx.y, tid = warp * 32 + lane;
+    const int frame = blockIdx.z;
+    const int X0 = blockIdx.x * PL_TW, Y0 = blockIdx.y * PL_TH;
+    const int Y1 = min(Y0 + PL_TH, p.H);
+    // source origin of the tile: the first tap of its first column, aligned down to 16 bytes (TMA), and of its first row
+    const int4 tq0 = __ldg(p.qtab + 2 * (X0 >> 2));
+    const int srcXw = tq0.x & ~3;                          // word index
+    const int srcY0 = __ldg(p.ytab + Y0).x;
+    if (USE_TMA) {
+        if (tid == 0) {
+            mbar_init(&bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            mbar_expect_tx(&bar, (uint32_t)(p.boxW * p.boxH));
+            tma_load_3d(sm, &tmap, &bar, srcXw * 4, srcY0, frame);
+        }
+    } else {
+        const uint8_t* g0 = p.dbgSrc + (long long)frame * p.dbgStride;
+        for (int i = tid; i < p.boxW * p.boxH; i += 256) {
+            const int r = i / p.boxW, c = i - r * p.boxW;
+            const int gx = srcXw * 4 + c, gy = srcY0 + r;
+            sm[i] = (gx < p.dbgW && gy < p.dbgH) ? g0[(long long)gy * p.dbgPitch + gx] : 0;
+        }
+    }
+    // this thread's four columns: taps from the host-made table, as in the fused kernel
+    const int gq = (X0 >> 2) + lane;
+    const bool active = 4 * gq < p.W;
+    const int4 t0 = active ? __ldg(p.qtab + 2 * gq) : tq0, t1 = active ? __ldg(p.qtab + 2 * gq + 1) : make_int4(0, 0, 0, 0);
+    const int wb = t0.x - srcXw;
+    const unsigned selLo01 = (unsigned)t0.y & 0xFFFFu, selHi01 = (unsigned)t0.y >> 16;
+    const unsigned selLo23 = (unsigned)t0.z & 0xFFFFu, selHi23 = (unsigned)t0.z >> 16;
+    const unsigned A0 = t1.x, A1 = t1.y, A2 = t1.z, A3 = t1.w;
+    const int spw = p.boxW >> 2;
+    // row band of this warp
+    const int rpw = (PL_TH + 7) / 8;
+    const int yb = Y0 + warp * rpw, ye = min(yb + rpw, Y1);
+    __syncthreads();
+    if (USE_TMA) mbar_wait(&bar, 0);
+    if (!active || yb >= ye) return;
+    const uint32_t* srcw = (const uint32_t*)sm + wb - srcY0 * spw;
+    auto hrow = [&](int srow, unsigned (&h)[4]) {
+        const uint32_t* r = srcw + srow * spw;
+        const unsigned w0 = r[0], w1 = r[1], w2 = r[2];
+        const unsigned B01 = __byte_perm(__byte_perm(w0, w1, selLo01), w2, selHi01);
+        const unsigned B23 = __byte_perm(__byte_perm(w0, w1, selLo23), w2, selHi23);
+        h[0] = __dp2a_lo(A0, B01, 0u) & ~15u;
+        h[1] = __dp2a_hi(A1, B01, 0u) & ~15u;
+        h[2] = __dp2a_lo(A2, B23, 0u) & ~15u;
+        h[3] = __dp2a_hi(A3, B23, 0u) & ~15u;
+    };
+    unsigned h0[4], h1[4] = { 0, 0, 0, 0 };
+    int prev1 = -1;
+    const bool fullX = 4 * gq + 4 <= p.W;
+    uint8_t* grow = p.dst + (long long)frame * p.dstFrameStride + (long long)yb * p.dstPitch + 4 * gq;
+    const int4* ryp = p.ytab + yb;
+#pragma unroll 1
+    for (int y = yb; y < ye; y++, ryp++, grow += p.dstPitch) {
+        const int4 ey = __ldg(ryp);                     // (the same address in every lane: one transaction; uniform control flow below)
+        if (ey.x == prev1) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) h0[i] = h1[i];
+        } else hrow(ey.x, h0);
+        if (ey.y != ey.x) hrow(ey.y, h1);
+        else {
+#pragma unroll
+            for (int i = 0; i < 4; i++) h1[i] = h0[i];
+        }
+        prev1 = ey.y;
+        const unsigned b0 = (unsigned)ey.z, b1 = (unsigned)ey.w;
+        unsigned word = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const unsigned v = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
+            word |= v << (8 * i);
+        }
+        if (fullX) *(uint32_t*)grow = word;
+        else {
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (4 * gq + i < p.W) grow[i] = (uint8_t)(word >> (8 * i));
+        }
+    }
+}
+
 } // namespace
 
 struct PyramidPlan {
@@ -224,6 +334,9 @@ struct PyramidPlan {
     PyrParams prm;
     int boxW, boxH;
     size_t smemBytes;
+    // per-level launches (batches): TMA box of a destination tile's source footprint, per level
+    bool lvOk = false;
+    int lvBoxW[OS1_MAX_LEVELS], lvBoxH[OS1_MAX_LEVELS];
     CUresult (*encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                        const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 };
@@ -369,6 +482,34 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         fn = nullptr;
     }
     P->encode = (decltype(P->encode))fn;
+    // per-level launches: the largest source footprint of a PL_TW x PL_TH destination tile, per level
+    P->lvOk = g.nlevels >= 2;
+    for (int l = 1; l < g.nlevels; l++) {
+        std::vector<short> s0, s1, c0, c1, t0, t1;
+        os1_host_resize_taps(g.lv[l - 1].w, g.lv[l].w, false, s0, s1, c0, c1);
+        os1_host_resize_taps(g.lv[l - 1].h, g.lv[l].h, true, t0, t1, c0, c1);
+        int bw = 16, bh = 1;
+        for (int X0 = 0; X0 < g.lv[l].w; X0 += PL_TW) {
+            const int X1 = std::min(X0 + PL_TW, g.lv[l].w);
+            const int first = ((int)s0[X0] >> 2 & ~3) * 4;                  // as the kernel aligns it
+            int last = 0;
+            for (int x = X0; x < X1; x++) last = std::max(last, (int)s1[x]);
+            // a group's three source words start at its first tap's word: the last group may read up to 11 bytes past its first tap
+            const int lastGroupFirst = ((int)s0[(X1 - 1) & ~3] >> 2) * 4;
+            last = std::max(last, lastGroupFirst + 11);
+            bw = std::max(bw, last + 1 - first);
+        }
+        for (int Y0 = 0; Y0 < g.lv[l].h; Y0 += PL_TH) {
+            const int Y1 = std::min(Y0 + PL_TH, g.lv[l].h);
+            int last = 0;
+            for (int y = Y0; y < Y1; y++) last = std::max(last, (int)t1[y]);
+            bh = std::max(bh, last + 1 - (int)t0[Y0]);
+        }
+        bw = (bw + 15) & ~15;
+        P->lvBoxW[l] = bw; P->lvBoxH[l] = bh;
+        if (bw > 256 || bh > 256 || (size_t)bw * bh + 256 > 200 * 1024) P->lvOk = false;
+    }
+    if (!P->tapsFit || !P->encode || P->cudaErr != cudaSuccess) P->lvOk = false;
     return P;
 }
 
@@ -384,9 +525,60 @@ void os1_pyramid_plan_destroy(PyramidPlan* P)
     delete P;
 }
 
+// batches: levels 1..L-1 one launch each (see pyramid_level_kernel)
+static cudaError_t launch_levels(PyramidPlan* P, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s)
+{
+    static const bool noTma = getenv("OS1_DEBUG_NOTMA") != nullptr;
+    for (int l = 1; l < g.nlevels; l++) {
+        const LevelGeom& S = g.lv[l - 1];
+        const LevelGeom& D = g.lv[l];
+        const uint8_t* src = l == 1 ? d.lvl0 : d.slab + S.off;
+        const long long srcStride = l == 1 ? d.lvl0FrameStride : g.slabBytes;
+        const int srcPitch = l == 1 ? d.lvl0Pitch : S.pitch;
+        CUtensorMap tmap;
+        cuuint64_t dims[3] = { (cuuint64_t)S.w, (cuuint64_t)S.h, (cuuint64_t)nframes };
+        cuuint64_t strides[2] = { (cuuint64_t)srcPitch, (cuuint64_t)srcStride };
+        cuuint32_t box[3] = { (cuuint32_t)P->lvBoxW[l], (cuuint32_t)P->lvBoxH[l], 1 };
+        cuuint32_t estr[3] = { 1, 1, 1 };
+        CUresult r = P->encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)src, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+        LvlParams p;
+        p.level = l; p.W = D.w; p.H = D.h; p.boxW = P->lvBoxW[l]; p.boxH = P->lvBoxH[l];
+        p.qtab = P->d_qtab + P->prm.qOff[l]; p.ytab = P->d_ytab + P->prm.yOff[l];
+        p.dst = d.slab + D.off; p.dstFrameStride = g.slabBytes; p.dstPitch = D.pitch;
+        p.dbgSrc = src; p.dbgStride = srcStride; p.dbgPitch = srcPitch; p.dbgW = S.w; p.dbgH = S.h;
+        const size_t smem = (size_t)p.boxW * p.boxH + 128;
+        if (smem > 48 * 1024) {
+            cudaError_t e = os1_optin_smem(noTma ? (const void*)pyramid_level_kernel<false> : (const void*)pyramid_level_kernel<true>);
+            if (e != cudaSuccess) return e;
+        }
+        dim3 grid((D.w + PL_TW - 1) / PL_TW, (D.h + PL_TH - 1) / PL_TH, nframes), block(32, 8);
+        if (noTma) pyramid_level_kernel<false><<<grid, block, smem, s>>>(tmap, p);
+        else pyramid_level_kernel<true><<<grid, block, smem, s>>>(tmap, p);
+    }
+    return cudaGetLastError();
+}
+
+bool os1_pyramid_plan_levels_ok(const PyramidPlan* P) { return P && P->lvOk; }
+
+// frames from which a batch takes the per-level launches (below, the fused chain's single launch wins: measured cross-over)
+static int levels_min_frames()
+{
+    static const int lvMin = getenv("OS1_PYR_LEVELS_MIN") ? atoi(getenv("OS1_PYR_LEVELS_MIN")) : 64;
+    return lvMin;
+}
+
+int os1_pyramid_launch_count(const PyramidPlan* P, const Geometry& g, int nframes)
+{
+    if (g.nlevels < 2) return 0;
+    return (P && P->lvOk && nframes >= levels_min_frames()) ? g.nlevels - 1 : 1;
+}
+
 cudaError_t os1_launch_pyramid(PyramidPlan* P, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s)
 {
     if (g.nlevels < 2) return cudaSuccess;
+    if (P && P->lvOk && nframes >= levels_min_frames()) return launch_levels(P, g, d, nframes, s);
     if (!os1_pyramid_plan_ok(P)) return cudaErrorNotSupported;
     CUtensorMap tmap;
     cuuint64_t dims[3] = { (cuuint64_t)g.cols, (cuuint64_t)g.rows, (cuuint64_t)nframes };
