@@ -215,15 +215,19 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
 // round trips).  For a batch the bytes were never the problem — a frame's pyramid is 10.6 MB of traffic even unfused, 1.6 us at
 // HBM speed — the instructions were: halo pixels recomputed at every level, upper levels of a tile too small for 256 threads, lanes
 // of one warp sitting in different row bands and diverging on the row-reuse logic (33 thread-instructions per output pixel).
-// Here level l is one launch over all frames: a CTA owns a 128 x PL_TH tile of the DESTINATION level, pulls the source footprint
-// of that tile in with one TMA tile load, and then a warp is a row band and a lane a group of four columns — every lane of a warp
-// walks the same rows, so the horizontally filtered source row is reused without any divergence and every output row of the tile
-// is one coalesced 128-byte store.  No pixel is computed twice; the source halo re-read is 4-5 %.
+// Here level l is one launch over all frames: a CTA owns a 128 x PL_TH tile of the DESTINATION level in TWO consecutive frames and
+// pulls the source footprints of both in with one TMA tile load (box depth 2).  A warp is a band of 16 rows; its lower half-warp
+// works on the first frame and its upper half-warp on the second, a lane on eight adjacent columns — both frames have the same
+// geometry, so every lane of a warp walks the same rows: the horizontally filtered source row is reused without any divergence,
+// the per-row bookkeeping is paid once per eight pixels, and every output row of a frame's tile is one 128-byte store.  No pixel
+// is computed twice; the source halo re-read is 4-5 %.
 #define PL_TW 128
-#define PL_TH 128
+#define PL_TH 64
+#define PL_WARPS 4
 struct LvlParams {
     int level;
     int W, H;                    // destination level
+    int nframes;
     int boxW, boxH;              // TMA box (source footprint of a tile, inner extent a multiple of 16 bytes)
     const int4* qtab;            // this level's QuadTaps (2 x int4 per group of four destination columns)
     const int4* ytab;            // this level's vertical taps per destination row
@@ -232,90 +236,105 @@ struct LvlParams {
 };
 
 template <bool USE_TMA>
-__global__ void __launch_bounds__(256, 6) pyramid_level_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ LvlParams p)
+__global__ void __launch_bounds__(32 * PL_WARPS, 7) pyramid_level_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ LvlParams p)
 {
     extern __shared__ __align__(128) uint8_t sm_raw[];
     uint8_t* sm = sm_raw + ((128u - ((unsigned)__cvta_generic_to_shared(sm_raw) & 127u)) & 127u);
     __shared__ __align__(8) uint64_t bar;
     const int lane = threadIdx.x, warp = threadIdx.y, tid = warp * 32 + lane;
-    const int frame = blockIdx.z;
+    const int half = lane >> 4, l16 = lane & 15;
+    const int frame0 = 2 * blockIdx.z, frame = frame0 + half;
     const int X0 = blockIdx.x * PL_TW, Y0 = blockIdx.y * PL_TH;
     const int Y1 = min(Y0 + PL_TH, p.H);
     // source origin of the tile: the first tap of its first column, aligned down to 16 bytes (TMA), and of its first row
     const int4 tq0 = __ldg(p.qtab + 2 * (X0 >> 2));
     const int srcXw = tq0.x & ~3;                          // word index
     const int srcY0 = __ldg(p.ytab + Y0).x;
+    const int plane = p.boxW * p.boxH;
     if (USE_TMA) {
         if (tid == 0) {
             mbar_init(&bar, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            mbar_expect_tx(&bar, (uint32_t)(p.boxW * p.boxH));
-            tma_load_3d(sm, &tmap, &bar, srcXw * 4, srcY0, frame);
+            mbar_expect_tx(&bar, (uint32_t)(2 * plane));                 // (a frame beyond the batch arrives as zeros, and counts)
+            tma_load_3d(sm, &tmap, &bar, srcXw * 4, srcY0, frame0);
         }
     } else {
-        const uint8_t* g0 = p.dbgSrc + (long long)frame * p.dbgStride;
-        for (int i = tid; i < p.boxW * p.boxH; i += 256) {
-            const int r = i / p.boxW, c = i - r * p.boxW;
+        for (int i = tid; i < 2 * plane; i += 32 * PL_WARPS) {
+            const int f = i / plane, j = i - f * plane;
+            const int r = j / p.boxW, c = j - r * p.boxW;
             const int gx = srcXw * 4 + c, gy = srcY0 + r;
-            sm[i] = (gx < p.dbgW && gy < p.dbgH) ? g0[(long long)gy * p.dbgPitch + gx] : 0;
+            sm[i] = (frame0 + f < p.nframes && gx < p.dbgW && gy < p.dbgH) ? p.dbgSrc[(long long)(frame0 + f) * p.dbgStride + (long long)gy * p.dbgPitch + gx] : 0;
         }
     }
-    // this thread's four columns: taps from the host-made table, as in the fused kernel
-    const int gq = (X0 >> 2) + lane;
-    const bool active = 4 * gq < p.W;
-    const int4 t0 = active ? __ldg(p.qtab + 2 * gq) : tq0, t1 = active ? __ldg(p.qtab + 2 * gq + 1) : make_int4(0, 0, 0, 0);
-    const int wb = t0.x - srcXw;
-    const unsigned selLo01 = (unsigned)t0.y & 0xFFFFu, selHi01 = (unsigned)t0.y >> 16;
-    const unsigned selLo23 = (unsigned)t0.z & 0xFFFFu, selHi23 = (unsigned)t0.z >> 16;
-    const unsigned A0 = t1.x, A1 = t1.y, A2 = t1.z, A3 = t1.w;
+    // this thread's eight columns = two groups of four: taps from the host-made table, as in the fused kernel
+    const int gq = (X0 >> 2) + 2 * l16;
+    const bool active = 4 * gq < p.W && frame < p.nframes;
+    const bool haveB = 4 * gq + 4 < p.W;
+    const int4 ta0 = active ? __ldg(p.qtab + 2 * gq) : tq0, ta1 = active ? __ldg(p.qtab + 2 * gq + 1) : make_int4(0, 0, 0, 0);
+    const int4 tb0 = (active && haveB) ? __ldg(p.qtab + 2 * gq + 2) : ta0, tb1 = (active && haveB) ? __ldg(p.qtab + 2 * gq + 3) : make_int4(0, 0, 0, 0);
     const int spw = p.boxW >> 2;
     // row band of this warp
-    const int rpw = (PL_TH + 7) / 8;
+    constexpr int rpw = PL_TH / PL_WARPS;
     const int yb = Y0 + warp * rpw, ye = min(yb + rpw, Y1);
     __syncthreads();
     if (USE_TMA) mbar_wait(&bar, 0);
     if (!active || yb >= ye) return;
-    const uint32_t* srcw = (const uint32_t*)sm + wb - srcY0 * spw;
-    auto hrow = [&](int srow, unsigned (&h)[4]) {
-        const uint32_t* r = srcw + srow * spw;
-        const unsigned w0 = r[0], w1 = r[1], w2 = r[2];
-        const unsigned B01 = __byte_perm(__byte_perm(w0, w1, selLo01), w2, selHi01);
-        const unsigned B23 = __byte_perm(__byte_perm(w0, w1, selLo23), w2, selHi23);
-        h[0] = __dp2a_lo(A0, B01, 0u) & ~15u;
-        h[1] = __dp2a_hi(A1, B01, 0u) & ~15u;
-        h[2] = __dp2a_lo(A2, B23, 0u) & ~15u;
-        h[3] = __dp2a_hi(A3, B23, 0u) & ~15u;
+    const uint32_t* srcA = (const uint32_t*)(sm + half * plane) + (ta0.x - srcXw) - srcY0 * spw;
+    const int dB = tb0.x - ta0.x;                          // group B's first source word relative to group A's
+    const unsigned selA01 = (unsigned)ta0.y & 0xFFFFu, selA01h = (unsigned)ta0.y >> 16, selA23 = (unsigned)ta0.z & 0xFFFFu, selA23h = (unsigned)ta0.z >> 16;
+    const unsigned selB01 = (unsigned)tb0.y & 0xFFFFu, selB01h = (unsigned)tb0.y >> 16, selB23 = (unsigned)tb0.z & 0xFFFFu, selB23h = (unsigned)tb0.z >> 16;
+    auto hrow = [&](int srow, unsigned (&h)[8]) {
+        const uint32_t* r = srcA + srow * spw;
+        const uint32_t* q = r + dB;
+        const unsigned a0 = r[0], a1 = r[1], a2 = r[2], b0 = q[0], b1 = q[1], b2 = q[2];
+        const unsigned A01 = __byte_perm(__byte_perm(a0, a1, selA01), a2, selA01h), A23 = __byte_perm(__byte_perm(a0, a1, selA23), a2, selA23h);
+        const unsigned B01 = __byte_perm(__byte_perm(b0, b1, selB01), b2, selB01h), B23 = __byte_perm(__byte_perm(b0, b1, selB23), b2, selB23h);
+        // H with its low four bits cleared: (c << 12) * (H & ~15) >> 32 == (c * (H >> 4)) >> 16, so the vertical pass is one
+        // multiply-high per tap
+        h[0] = __dp2a_lo((unsigned)ta1.x, A01, 0u) & ~15u;
+        h[1] = __dp2a_hi((unsigned)ta1.y, A01, 0u) & ~15u;
+        h[2] = __dp2a_lo((unsigned)ta1.z, A23, 0u) & ~15u;
+        h[3] = __dp2a_hi((unsigned)ta1.w, A23, 0u) & ~15u;
+        h[4] = __dp2a_lo((unsigned)tb1.x, B01, 0u) & ~15u;
+        h[5] = __dp2a_hi((unsigned)tb1.y, B01, 0u) & ~15u;
+        h[6] = __dp2a_lo((unsigned)tb1.z, B23, 0u) & ~15u;
+        h[7] = __dp2a_hi((unsigned)tb1.w, B23, 0u) & ~15u;
     };
-    unsigned h0[4], h1[4] = { 0, 0, 0, 0 };
+    unsigned h0[8], h1[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
     int prev1 = -1;
-    const bool fullX = 4 * gq + 4 <= p.W;
-    uint8_t* grow = p.dst + (long long)frame * p.dstFrameStride + (long long)yb * p.dstPitch + 4 * gq;
+    const int ncols = min(8, p.W - 4 * gq);
+    unsigned off = (unsigned)yb * (unsigned)p.dstPitch + 4u * (unsigned)gq;
+    uint8_t* const dframe = p.dst + (long long)frame * p.dstFrameStride;
     const int4* ryp = p.ytab + yb;
+    int4 eyNext = __ldg(ryp);                           // (the same address in every lane: one transaction; uniform control flow below)
 #pragma unroll 1
-    for (int y = yb; y < ye; y++, ryp++, grow += p.dstPitch) {
-        const int4 ey = __ldg(ryp);                     // (the same address in every lane: one transaction; uniform control flow below)
+    for (int y = yb; y < ye; y++, off += (unsigned)p.dstPitch) {
+        const int4 ey = eyNext;
+        eyNext = __ldg(++ryp);                          // the next row's taps travel while this row is computed (the table has a spare entry at its end)
         if (ey.x == prev1) {
 #pragma unroll
-            for (int i = 0; i < 4; i++) h0[i] = h1[i];
+            for (int i = 0; i < 8; i++) h0[i] = h1[i];
         } else hrow(ey.x, h0);
         if (ey.y != ey.x) hrow(ey.y, h1);
         else {
 #pragma unroll
-            for (int i = 0; i < 4; i++) h1[i] = h0[i];
+            for (int i = 0; i < 8; i++) h1[i] = h0[i];
         }
         prev1 = ey.y;
-        const unsigned b0 = (unsigned)ey.z, b1 = (unsigned)ey.w;
-        unsigned word = 0;
+        const unsigned c0 = (unsigned)ey.z, c1 = (unsigned)ey.w;
+        unsigned word[2] = { 0, 0 };
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const unsigned v = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
-            word |= v << (8 * i);
+        for (int i = 0; i < 8; i++) {
+            // ((c0*(H0>>4))>>16) + ((c1*(H1>>4))>>16) + 2) >> 2, each product taken as a multiply-high
+            const unsigned v = (__umulhi(c0, h0[i]) + __umulhi(c1, h1[i]) + 2u) >> 2;
+            word[i >> 2] |= v << (8 * (i & 3));
         }
-        if (fullX) *(uint32_t*)grow = word;
+        uint8_t* grow = dframe + off;
+        if (ncols == 8) *(uint2*)grow = make_uint2(word[0], word[1]);
         else {
 #pragma unroll
-            for (int i = 0; i < 4; i++)
-                if (4 * gq + i < p.W) grow[i] = (uint8_t)(word >> (8 * i));
+            for (int i = 0; i < 8; i++)
+                if (i < ncols) grow[i] = (uint8_t)(word[i >> 2] >> (8 * (i & 3)));
         }
     }
 }
@@ -451,7 +470,7 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
             os1_host_resize_taps(g.lv[l - 1].h, g.lv[l].h, true, s0, s1, c0, c1);
             for (int y = 0; y < g.lv[l].h; y++) yt4.push_back(make_int4(s0[y], s1[y], (int)c0[y] << 12, (int)c1[y] << 12));
         }
-        if (yt4.empty()) yt4.push_back(make_int4(0, 0, 0, 0));
+        yt4.push_back(make_int4(0, 0, 0, 0));           // spare entry: pyramid_level_kernel reads one row ahead
         upload(P->d_ytab, yt4);
         p.ytab = P->d_ytab;
         if (q.empty()) q.push_back(make_int4(0, 0, 0, 0));
@@ -507,7 +526,7 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         }
         bw = (bw + 15) & ~15;
         P->lvBoxW[l] = bw; P->lvBoxH[l] = bh;
-        if (bw > 256 || bh > 256 || (size_t)bw * bh + 256 > 200 * 1024) P->lvOk = false;
+        if (bw > 256 || bh > 256 || 2 * (size_t)bw * bh + 256 > 200 * 1024) P->lvOk = false;
     }
     if (!P->tapsFit || !P->encode || P->cudaErr != cudaSuccess) P->lvOk = false;
     return P;
@@ -538,22 +557,22 @@ static cudaError_t launch_levels(PyramidPlan* P, const Geometry& g, const DevPtr
         CUtensorMap tmap;
         cuuint64_t dims[3] = { (cuuint64_t)S.w, (cuuint64_t)S.h, (cuuint64_t)nframes };
         cuuint64_t strides[2] = { (cuuint64_t)srcPitch, (cuuint64_t)srcStride };
-        cuuint32_t box[3] = { (cuuint32_t)P->lvBoxW[l], (cuuint32_t)P->lvBoxH[l], 1 };
+        cuuint32_t box[3] = { (cuuint32_t)P->lvBoxW[l], (cuuint32_t)P->lvBoxH[l], 2 };           // two frames per CTA
         cuuint32_t estr[3] = { 1, 1, 1 };
         CUresult r = P->encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)src, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
         LvlParams p;
-        p.level = l; p.W = D.w; p.H = D.h; p.boxW = P->lvBoxW[l]; p.boxH = P->lvBoxH[l];
+        p.level = l; p.W = D.w; p.H = D.h; p.nframes = nframes; p.boxW = P->lvBoxW[l]; p.boxH = P->lvBoxH[l];
         p.qtab = P->d_qtab + P->prm.qOff[l]; p.ytab = P->d_ytab + P->prm.yOff[l];
         p.dst = d.slab + D.off; p.dstFrameStride = g.slabBytes; p.dstPitch = D.pitch;
         p.dbgSrc = src; p.dbgStride = srcStride; p.dbgPitch = srcPitch; p.dbgW = S.w; p.dbgH = S.h;
-        const size_t smem = (size_t)p.boxW * p.boxH + 128;
+        const size_t smem = 2 * (size_t)p.boxW * p.boxH + 128;
         if (smem > 48 * 1024) {
             cudaError_t e = os1_optin_smem(noTma ? (const void*)pyramid_level_kernel<false> : (const void*)pyramid_level_kernel<true>);
             if (e != cudaSuccess) return e;
         }
-        dim3 grid((D.w + PL_TW - 1) / PL_TW, (D.h + PL_TH - 1) / PL_TH, nframes), block(32, 8);
+        dim3 grid((D.w + PL_TW - 1) / PL_TW, (D.h + PL_TH - 1) / PL_TH, (nframes + 1) / 2), block(32, PL_WARPS);
         if (noTma) pyramid_level_kernel<false><<<grid, block, smem, s>>>(tmap, p);
         else pyramid_level_kernel<true><<<grid, block, smem, s>>>(tmap, p);
     }

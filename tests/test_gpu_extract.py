@@ -194,3 +194,47 @@ def test_full_size_properties_1080p_batch():
         w, h = e.level_size(l)
         assert x.min() >= 19 - 1e-3 and y.min() >= 19 - 1e-3 and x.max() <= w - 20 + 1e-3 and y.max() <= h - 20 + 1e-3
     assert (k["response"] >= 7).all() and (k["angle"] >= 0).all() and (k["angle"] < 360).all()
+
+
+@pytest.mark.parametrize("shape,nf,sf,nl,seed", [((240, 320), 500, 1.2, 8, 70), ((333, 517), 700, 1.2, 8, 71), ((300, 420), 400, 1.5, 5, 72),
+                                                 ((131, 257), 300, 1.2, 6, 73)])
+def test_per_level_pyramid_launches_for_batches(oracle_lib, shape, nf, sf, nl, seed):
+    """Batches of 64 frames or more build the pyramid with one launch per level (csrc/pyramid.cu: pyramid_level_kernel) instead of
+    the fused chain: same bytes at every level (tiles cut by the image edge, images narrower than a tile, a tile row of one
+    pixel row), and the same keypoints and descriptors as the frames extracted one by one."""
+    import torch
+    from os1_b200 import KEYPOINT_DTYPE
+    B = 66
+    frames = synth.video(B, shape[0], shape[1], seed=seed)
+    e = gpu_ext(nf, sf, nl, 20, 7)
+    cap = e.max_keypoints()
+    fd = torch.from_numpy(frames).cuda()
+    kp = torch.zeros((B, cap, 28), dtype=torch.uint8, device="cuda"); desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+    cnt = torch.zeros(B, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    e.extract_batch_raw(fd.data_ptr(), B, shape[0], shape[1], shape[1], shape[0] * shape[1], True, kp.data_ptr(), desc.data_ptr(), cap, cnt.data_ptr(), True)
+    e.synchronize()
+    assert e.launches_per_call() == (nl - 1) + 3, "the batch did not take the per-level launches"
+    o = oracle_lib.Oracle(nf, sf, nl, 20, 7)
+    for f in (0, 1, B // 2, B - 1):
+        ko, do = o.extract(frames[f])
+        for l in range(nl):
+            assert np.array_equal(o.level_pixels(l), e.pyramid_level(l, f)), "frame %d pyramid level %d" % (f, l)
+        n = int(cnt[f])
+        assert n == len(ko)
+        k = kp[f, :n].cpu().numpy().view(KEYPOINT_DTYPE).reshape(-1)
+        assert np.array_equal(k["x"], ko[:, 0]) and np.array_equal(k["y"], ko[:, 1]) and np.array_equal(k["angle"], ko[:, 3])
+        assert np.array_equal(desc[f, :n].cpu().numpy(), do)
+    # the fused chain on the same frames (a batch below the threshold)
+    kq, dq, cq = e.extract_batch(frames[:5])
+    assert e.launches_per_call() == 4
+    for f in range(5):
+        n = int(cnt[f])
+        assert cq[f] == n and np.array_equal(dq[f, :n], desc[f, :n].cpu().numpy())
+    # host frames: the chunked pipeline (chunks of up to 64 frames, so both paths inside one call)
+    kh, dh, ch = e.extract_batch(frames)
+    assert np.array_equal(ch, cnt.cpu().numpy())
+    dd = desc.cpu().numpy()
+    for f in range(B):
+        assert np.array_equal(dh[f, :ch[f]], dd[f, :ch[f]]), "frame %d" % f
+    e.close()
