@@ -300,42 +300,55 @@ __global__ void __launch_bounds__(32 * PL_WARPS, 7) pyramid_level_kernel(const _
         h[6] = __dp2a_lo((unsigned)tb1.z, B23, 0u) & ~15u;
         h[7] = __dp2a_hi((unsigned)tb1.w, B23, 0u) & ~15u;
     };
-    unsigned h0[8], h1[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
-    int prev1 = -1;
     const int ncols = min(8, p.W - 4 * gq);
-    unsigned off = (unsigned)yb * (unsigned)p.dstPitch + 4u * (unsigned)gq;
-    uint8_t* const dframe = p.dst + (long long)frame * p.dstFrameStride;
-    const int4* ryp = p.ytab + yb;
-    int4 eyNext = __ldg(ryp);                           // (the same address in every lane: one transaction; uniform control flow below)
-#pragma unroll 1
-    for (int y = yb; y < ye; y++, off += (unsigned)p.dstPitch) {
-        const int4 ey = eyNext;
-        eyNext = __ldg(++ryp);                          // the next row's taps travel while this row is computed (the table has a spare entry at its end)
-        if (ey.x == prev1) {
+    uint8_t* grow = p.dst + (long long)frame * p.dstFrameStride + (long long)yb * p.dstPitch + 4 * gq;
+    // one destination row from two filtered source rows: ((c0*(H0>>4))>>16) + ((c1*(H1>>4))>>16) + 2) >> 2, each product taken as
+    // a multiply-high; the four sums of a word (<= 1022 each) are shifted and packed two at a time in 16-bit lanes
+    auto emit = [&](const unsigned (&top)[8], const unsigned (&bot)[8], unsigned c0, unsigned c1) {
+        unsigned word[2];
 #pragma unroll
-            for (int i = 0; i < 8; i++) h0[i] = h1[i];
-        } else hrow(ey.x, h0);
-        if (ey.y != ey.x) hrow(ey.y, h1);
-        else {
+        for (int k = 0; k < 2; k++) {
+            unsigned sum[4];
 #pragma unroll
-            for (int i = 0; i < 8; i++) h1[i] = h0[i];
+            for (int i = 0; i < 4; i++) sum[i] = __umulhi(c0, top[4 * k + i]) + __umulhi(c1, bot[4 * k + i]) + 2u;
+            const unsigned ev = sum[0] + (sum[2] << 16), od = sum[1] + (sum[3] << 16);
+            word[k] = ((ev >> 2) & 0x00FF00FFu) | ((od << 6) & 0xFF00FF00u);
         }
-        prev1 = ey.y;
-        const unsigned c0 = (unsigned)ey.z, c1 = (unsigned)ey.w;
-        unsigned word[2] = { 0, 0 };
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            // ((c0*(H0>>4))>>16) + ((c1*(H1>>4))>>16) + 2) >> 2, each product taken as a multiply-high
-            const unsigned v = (__umulhi(c0, h0[i]) + __umulhi(c1, h1[i]) + 2u) >> 2;
-            word[i >> 2] |= v << (8 * (i & 3));
-        }
-        uint8_t* grow = dframe + off;
         if (ncols == 8) *(uint2*)grow = make_uint2(word[0], word[1]);
         else {
 #pragma unroll
             for (int i = 0; i < 8; i++)
                 if (i < ncols) grow[i] = (uint8_t)(word[i >> 2] >> (8 * (i & 3)));
         }
+        grow += p.dstPitch;
+    };
+    // The loop steps through the SOURCE rows of the band, filtering each once into one of two register sets used alternately
+    // (the loop is unrolled by two, so which set holds which row is static and nothing is ever copied); a destination row is
+    // emitted at the step that filters its second source row — its first is the row of the step before (the plan checks
+    // that the second source rows of a level increase strictly), or the same row where cv::resize clamps at the last row.
+    const int4* ryp = p.ytab + yb;
+    int4 ey = __ldg(ryp), eyNext = __ldg(ryp + 1);       // (the same address in every lane; the table has two spare entries at its end)
+    int srow = ey.x, left = ye - yb;
+    unsigned hA[8], hB[8];
+    const int srowEnd = srcY0 + p.boxH;                  // (never reached: the band's last row is emitted inside the box; a bound all the same)
+#pragma unroll 1
+    while (srow < srowEnd) {
+        hrow(srow, hA);
+        if (srow == ey.y) {
+            if (ey.x == ey.y) emit(hA, hA, (unsigned)ey.z, (unsigned)ey.w);
+            else emit(hB, hA, (unsigned)ey.z, (unsigned)ey.w);
+            if (--left == 0) break;
+            ey = eyNext; ryp++; eyNext = __ldg(ryp + 1);
+        }
+        srow++;
+        hrow(srow, hB);
+        if (srow == ey.y) {
+            if (ey.x == ey.y) emit(hB, hB, (unsigned)ey.z, (unsigned)ey.w);
+            else emit(hA, hB, (unsigned)ey.z, (unsigned)ey.w);
+            if (--left == 0) break;
+            ey = eyNext; ryp++; eyNext = __ldg(ryp + 1);
+        }
+        srow++;
     }
 }
 
@@ -470,7 +483,8 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
             os1_host_resize_taps(g.lv[l - 1].h, g.lv[l].h, true, s0, s1, c0, c1);
             for (int y = 0; y < g.lv[l].h; y++) yt4.push_back(make_int4(s0[y], s1[y], (int)c0[y] << 12, (int)c1[y] << 12));
         }
-        yt4.push_back(make_int4(0, 0, 0, 0));           // spare entry: pyramid_level_kernel reads one row ahead
+        yt4.push_back(make_int4(0, 0, 0, 0));           // spare entries: pyramid_level_kernel reads two rows ahead
+        yt4.push_back(make_int4(0, 0, 0, 0));
         upload(P->d_ytab, yt4);
         p.ytab = P->d_ytab;
         if (q.empty()) q.push_back(make_int4(0, 0, 0, 0));
@@ -518,6 +532,8 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
             last = std::max(last, lastGroupFirst + 11);
             bw = std::max(bw, last + 1 - first);
         }
+        for (int y = 1; y < g.lv[l].h; y++)
+            if (t1[y] <= t1[y - 1]) P->lvOk = false;      // (the kernel emits at most one destination row per source row)
         for (int Y0 = 0; Y0 < g.lv[l].h; Y0 += PL_TH) {
             const int Y1 = std::min(Y0 + PL_TH, g.lv[l].h);
             int last = 0;

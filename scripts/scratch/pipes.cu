@@ -32,6 +32,18 @@ __global__ void __launch_bounds__(256) k(unsigned seed, int iters, unsigned* sin
             if (MODE == 1 || MODE == 2) { h[i] = hmin2(h[i], g[(i + 1) & 7]); g[i] = hmax2(g[i], h[(i + 3) & 7]); }
             if (MODE == 3 || MODE == 4) { h[i] = hrelu(h[i], one, g[(i + 1) & 7]); g[i] = hadd2u(g[i], h[(i + 3) & 7]); }
             if (MODE == 5) { a[i] = umin2(umin2(a[i], b[(i + 1) & 7]), b[(i + 2) & 7]); b[i] = umax2(umax2(b[i], a[(i + 3) & 7]), a[(i + 5) & 7]); }
+            if (MODE == 7 || MODE == 11) { a[i] = a[i] * b[(i + 1) & 7] + b[(i + 2) & 7]; b[i] = b[i] * a[(i + 3) & 7] + a[(i + 5) & 7]; }
+            if (MODE == 8 || MODE == 10) { a[i] = __umulhi(a[i], b[(i + 1) & 7]); b[i] = __umulhi(b[i], a[(i + 3) & 7]); }
+            if (MODE == 9) { a[i] = __dp2a_lo(a[i], b[(i + 1) & 7], b[(i + 2) & 7]); b[i] = __dp2a_hi(b[i], a[(i + 3) & 7], a[(i + 5) & 7]); }
+            if (MODE == 10) { h[i] = umin2(h[i], g[(i + 1) & 7]); g[i] = umax2(g[i], h[(i + 3) & 7]); }
+            if (MODE == 11) { h[i] = __float_as_uint(__fmaf_rn(__uint_as_float(h[i]), 1.0001f, __uint_as_float(g[(i + 1) & 7]))); g[i] = __float_as_uint(__fmaf_rn(__uint_as_float(g[i]), 0.9999f, __uint_as_float(h[(i + 3) & 7]))); }
+            if (MODE == 12) { a[i] = __byte_perm(a[i], b[(i + 1) & 7], b[(i + 2) & 7]); b[i] = __byte_perm(b[i], a[(i + 3) & 7], a[(i + 5) & 7]); }
+            if (MODE == 15) { a[i] = __byte_perm(a[i], b[(i + 1) & 7], 0x5140); b[i] = __byte_perm(b[i], a[(i + 3) & 7], 0x7250); }
+            if (MODE == 16) { a[i] = __byte_perm(a[i], b[(i + 1) & 7], 0x5140); b[i] = __byte_perm(b[i], a[(i + 3) & 7], 0x7250); h[i] = umin2(h[i], g[(i + 1) & 7]); g[i] = umax2(g[i], h[(i + 3) & 7]); }
+            if (MODE == 17) { a[i] = (a[i] & b[(i + 1) & 7]) | (b[(i + 2) & 7] & ~a[i]); b[i] = b[i] ^ a[(i + 3) & 7] ^ a[(i + 5) & 7]; }
+            if (MODE == 18) { a[i] = a[i] + b[(i + 1) & 7] + b[(i + 2) & 7]; b[i] = b[i] + a[(i + 3) & 7] - a[(i + 5) & 7]; }
+            if (MODE == 13) { a[i] = __funnelshift_r(a[i], b[(i + 1) & 7], 7); b[i] = __funnelshift_r(b[i], a[(i + 3) & 7], 9); }
+            if (MODE == 14) { h[i] = __float_as_uint(__fmaf_rn(__uint_as_float(h[i]), 1.0001f, __uint_as_float(g[(i + 1) & 7]))); g[i] = __float_as_uint(__fmaf_rn(__uint_as_float(g[i]), 0.9999f, __uint_as_float(h[(i + 3) & 7]))); }
             if (MODE == 6) { a[i] = __float_as_uint(fmn(__uint_as_float(a[i]), __uint_as_float(b[(i + 1) & 7]))); b[i] = __float_as_uint(fmaxf(__uint_as_float(b[i]), __uint_as_float(a[(i + 3) & 7]))); }
         }
     }
@@ -68,5 +80,17 @@ int main()
     run<4>("u16x2 + (fma.relu, add).f16x2", 32);
     run<5>("3-input u16x2 (VIMNMX3)", 16);
     run<6>("fminf/fmaxf (FMNMX)", 16);
+    run<7>("IMAD (32-bit mad.lo)", 16);
+    run<8>("IMAD.HI (umulhi)", 16);
+    run<9>("IDP.2A (dp2a)", 16);
+    run<10>("IMAD.HI + VIMNMX.U16x2", 32);
+    run<14>("FFMA", 16);
+    run<11>("IMAD + FFMA side by side", 32);
+    run<12>("PRMT", 16);
+    run<13>("SHF (funnel shift)", 16);
+    run<15>("PRMT, immediate selector", 16);
+    run<16>("PRMT imm + VIMNMX.U16x2", 32);
+    run<17>("LOP3", 16);
+    run<18>("IADD3", 16);
     return 0;
 }
