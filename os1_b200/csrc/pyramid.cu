@@ -159,12 +159,11 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
                     const unsigned w0 = r[0], w1 = r[1], w2 = r[2];
                     const unsigned B01 = __byte_perm(__byte_perm(w0, w1, selLo01), w2, selHi01);
                     const unsigned B23 = __byte_perm(__byte_perm(w0, w1, selLo23), w2, selHi23);
-                    // H with its low four bits cleared: (c << 12) * (H & ~15) >> 32 == (c * (H >> 4)) >> 16, so the
-                    // vertical pass is one multiply-high per tap
-                    h[0] = __dp2a_lo(A0, B01, 0u) & ~15u;
-                    h[1] = __dp2a_hi(A1, B01, 0u) & ~15u;
-                    h[2] = __dp2a_lo(A2, B23, 0u) & ~15u;
-                    h[3] = __dp2a_hi(A3, B23, 0u) & ~15u;
+                    // kept as H >> 4, what cv::resize's vertical pass multiplies
+                    h[0] = __dp2a_lo(A0, B01, 0u) >> 4;
+                    h[1] = __dp2a_hi(A1, B01, 0u) >> 4;
+                    h[2] = __dp2a_lo(A2, B23, 0u) >> 4;
+                    h[3] = __dp2a_hi(A3, B23, 0u) >> 4;
                 };
                 unsigned h0[4], h1[4] = { 0, 0, 0, 0 };
                 int prev1 = -1;
@@ -185,12 +184,13 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
                         for (int i = 0; i < 4; i++) h1[i] = h0[i];
                     }
                     prev1 = ey.y;
-                    const unsigned b0 = (unsigned)ey.z, b1 = (unsigned)ey.w;
+                    const unsigned b0 = (unsigned)ey.z >> 12, b1 = (unsigned)ey.w >> 12;
                     unsigned word = 0;
 #pragma unroll
                     for (int i = 0; i < 4; i++) {
-                        // ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2, each product taken as a multiply-high
-                        const unsigned v = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;
+                        // ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2: full 32-bit products (< 2^26), their upper halves
+                        // summed by dp2a against the byte pair (0, 1) — a multiply-high runs at half the rate of these
+                        const unsigned v = __dp2a_lo(b1 * h1[i], 0x0100u, __dp2a_lo(b0 * h0[i], 0x0100u, 2u)) >> 2;
                         word |= v << (8 * i);
                     }
                     *dp = word;
@@ -216,11 +216,11 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
 // HBM speed — the instructions were: halo pixels recomputed at every level, upper levels of a tile too small for 256 threads, lanes
 // of one warp sitting in different row bands and diverging on the row-reuse logic (33 thread-instructions per output pixel).
 // Here level l is one launch over all frames: a CTA owns a 128 x PL_TH tile of the DESTINATION level in TWO consecutive frames and
-// pulls the source footprints of both in with one TMA tile load (box depth 2).  A warp is a band of 16 rows; its lower half-warp
-// works on the first frame and its upper half-warp on the second, a lane on eight adjacent columns — both frames have the same
-// geometry, so every lane of a warp walks the same rows: the horizontally filtered source row is reused without any divergence,
-// the per-row bookkeeping is paid once per eight pixels, and every output row of a frame's tile is one 128-byte store.  No pixel
-// is computed twice; the source halo re-read is 4-5 %.
+// pulls the source footprints of both in with one TMA tile load (box depth 2).  A warp is a band of 16 rows and a lane a group of
+// four adjacent columns IN BOTH FRAMES — the two frames have the same geometry, so a lane's taps, selectors and coefficients
+// serve eight pixels, every lane of a warp walks the same rows (the horizontally filtered source row is reused without any
+// divergence), the per-row bookkeeping is paid once per eight pixels, and every output row of a frame's tile is one 128-byte
+// store.  No pixel is computed twice; the source halo re-read is 4-5 %.
 #define PL_TW 128
 #define PL_TH 64
 #define PL_WARPS 4
@@ -229,7 +229,8 @@ struct LvlParams {
     int W, H;                    // destination level
     int nframes;
     int boxW, boxH;              // TMA box (source footprint of a tile, inner extent a multiple of 16 bytes)
-    const int4* qtab;            // this level's QuadTaps (2 x int4 per group of four destination columns)
+    const int4* qtab;            // this level's QuadTaps (2 x int4 per group of four destination columns): the coefficients
+    const int4* ptab;            // this level's PairTaps (1 x int4 per group): source words and byte selectors
     const int4* ytab;            // this level's vertical taps per destination row
     uint8_t* dst; long long dstFrameStride; int dstPitch;
     const uint8_t* dbgSrc; long long dbgStride; int dbgPitch, dbgW, dbgH;
@@ -242,8 +243,7 @@ __global__ void __launch_bounds__(32 * PL_WARPS, 7) pyramid_level_kernel(const _
     uint8_t* sm = sm_raw + ((128u - ((unsigned)__cvta_generic_to_shared(sm_raw) & 127u)) & 127u);
     __shared__ __align__(8) uint64_t bar;
     const int lane = threadIdx.x, warp = threadIdx.y, tid = warp * 32 + lane;
-    const int half = lane >> 4, l16 = lane & 15;
-    const int frame0 = 2 * blockIdx.z, frame = frame0 + half;
+    const int frame0 = 2 * blockIdx.z;
     const int X0 = blockIdx.x * PL_TW, Y0 = blockIdx.y * PL_TH;
     const int Y1 = min(Y0 + PL_TH, p.H);
     // source origin of the tile: the first tap of its first column, aligned down to 16 bytes (TMA), and of its first row
@@ -266,59 +266,71 @@ __global__ void __launch_bounds__(32 * PL_WARPS, 7) pyramid_level_kernel(const _
             sm[i] = (frame0 + f < p.nframes && gx < p.dbgW && gy < p.dbgH) ? p.dbgSrc[(long long)(frame0 + f) * p.dbgStride + (long long)gy * p.dbgPitch + gx] : 0;
         }
     }
-    // this thread's eight columns = two groups of four: taps from the host-made table, as in the fused kernel
-    const int gq = (X0 >> 2) + 2 * l16;
-    const bool active = 4 * gq < p.W && frame < p.nframes;
-    const bool haveB = 4 * gq + 4 < p.W;
-    const int4 ta0 = active ? __ldg(p.qtab + 2 * gq) : tq0, ta1 = active ? __ldg(p.qtab + 2 * gq + 1) : make_int4(0, 0, 0, 0);
-    const int4 tb0 = (active && haveB) ? __ldg(p.qtab + 2 * gq + 2) : ta0, tb1 = (active && haveB) ? __ldg(p.qtab + 2 * gq + 3) : make_int4(0, 0, 0, 0);
-    const int spw = p.boxW >> 2;
+    // this thread's four columns (two pixel pairs) in BOTH frames: coefficients and tap positions from the host-made tables
+    const int gq = (X0 >> 2) + lane;
+    const bool active = 4 * gq < p.W;
+    const int4 ta1 = active ? __ldg(p.qtab + 2 * gq + 1) : make_int4(0, 0, 0, 0);
+    const int4 pa = active ? __ldg(p.ptab + gq) : make_int4(srcXw, srcXw, 0, 0);
+    const int spw = p.boxW >> 2, planeW = plane >> 2;
     // row band of this warp
     constexpr int rpw = PL_TH / PL_WARPS;
     const int yb = Y0 + warp * rpw, ye = min(yb + rpw, Y1);
     __syncthreads();
     if (USE_TMA) mbar_wait(&bar, 0);
     if (!active || yb >= ye) return;
-    const uint32_t* srcA = (const uint32_t*)(sm + half * plane) + (ta0.x - srcXw) - srcY0 * spw;
-    const int dB = tb0.x - ta0.x;                          // group B's first source word relative to group A's
-    const unsigned selA01 = (unsigned)ta0.y & 0xFFFFu, selA01h = (unsigned)ta0.y >> 16, selA23 = (unsigned)ta0.z & 0xFFFFu, selA23h = (unsigned)ta0.z >> 16;
-    const unsigned selB01 = (unsigned)tb0.y & 0xFFFFu, selB01h = (unsigned)tb0.y >> 16, selB23 = (unsigned)tb0.z & 0xFFFFu, selB23h = (unsigned)tb0.z >> 16;
-    auto hrow = [&](int srow, unsigned (&h)[8]) {
-        const uint32_t* r = srcA + srow * spw;
-        const uint32_t* q = r + dB;
-        const unsigned a0 = r[0], a1 = r[1], a2 = r[2], b0 = q[0], b1 = q[1], b2 = q[2];
-        const unsigned A01 = __byte_perm(__byte_perm(a0, a1, selA01), a2, selA01h), A23 = __byte_perm(__byte_perm(a0, a1, selA23), a2, selA23h);
-        const unsigned B01 = __byte_perm(__byte_perm(b0, b1, selB01), b2, selB01h), B23 = __byte_perm(__byte_perm(b0, b1, selB23), b2, selB23h);
-        // H with its low four bits cleared: (c << 12) * (H & ~15) >> 32 == (c * (H >> 4)) >> 16, so the vertical pass is one
-        // multiply-high per tap
-        h[0] = __dp2a_lo((unsigned)ta1.x, A01, 0u) & ~15u;
-        h[1] = __dp2a_hi((unsigned)ta1.y, A01, 0u) & ~15u;
-        h[2] = __dp2a_lo((unsigned)ta1.z, A23, 0u) & ~15u;
-        h[3] = __dp2a_hi((unsigned)ta1.w, A23, 0u) & ~15u;
-        h[4] = __dp2a_lo((unsigned)tb1.x, B01, 0u) & ~15u;
-        h[5] = __dp2a_hi((unsigned)tb1.y, B01, 0u) & ~15u;
-        h[6] = __dp2a_lo((unsigned)tb1.z, B23, 0u) & ~15u;
-        h[7] = __dp2a_hi((unsigned)tb1.w, B23, 0u) & ~15u;
+    const unsigned sel01 = (unsigned)pa.z & 0xFFFFu, sel23 = (unsigned)pa.z >> 16;
+    const int4* ryp = p.ytab + yb;
+    int4 ey = __ldg(ryp), eyNext = __ldg(ryp + 1);       // (the same address in every lane; the table has two spare entries at its end)
+    int srow = ey.x, left = ye - yb;
+    // the two pairs' first source words in the current source row of the first frame (the second frame's plane follows the
+    // first's; the pointers step down a row after each filtered row)
+    const uint32_t* rowp = (const uint32_t*)sm + (srow - srcY0) * spw - srcXw;
+    const uint32_t *p01 = rowp + pa.x, *p23 = rowp + pa.y;
+    auto hrow = [&](unsigned (&h)[8]) {
+        const unsigned a0 = p01[0], a1 = p01[1], a2 = p23[0], a3 = p23[1];
+        const unsigned b0 = p01[planeW], b1 = p01[planeW + 1], b2 = p23[planeW], b3 = p23[planeW + 1];
+        p01 += spw; p23 += spw;
+        const unsigned A01 = __byte_perm(a0, a1, sel01), A23 = __byte_perm(a2, a3, sel23);
+        const unsigned B01 = __byte_perm(b0, b1, sel01), B23 = __byte_perm(b2, b3, sel23);
+        // kept as H >> 4, what cv::resize's vertical pass multiplies
+        h[0] = __dp2a_lo((unsigned)ta1.x, A01, 0u) >> 4;
+        h[1] = __dp2a_hi((unsigned)ta1.y, A01, 0u) >> 4;
+        h[2] = __dp2a_lo((unsigned)ta1.z, A23, 0u) >> 4;
+        h[3] = __dp2a_hi((unsigned)ta1.w, A23, 0u) >> 4;
+        h[4] = __dp2a_lo((unsigned)ta1.x, B01, 0u) >> 4;
+        h[5] = __dp2a_hi((unsigned)ta1.y, B01, 0u) >> 4;
+        h[6] = __dp2a_lo((unsigned)ta1.z, B23, 0u) >> 4;
+        h[7] = __dp2a_hi((unsigned)ta1.w, B23, 0u) >> 4;
     };
-    const int ncols = min(8, p.W - 4 * gq);
-    uint8_t* grow = p.dst + (long long)frame * p.dstFrameStride + (long long)yb * p.dstPitch + 4 * gq;
-    // one destination row from two filtered source rows: ((c0*(H0>>4))>>16) + ((c1*(H1>>4))>>16) + 2) >> 2, each product taken as
-    // a multiply-high; the four sums of a word (<= 1022 each) are shifted and packed two at a time in 16-bit lanes
-    auto emit = [&](const unsigned (&top)[8], const unsigned (&bot)[8], unsigned c0, unsigned c1) {
+    const int ncols = min(4, p.W - 4 * gq);
+    const bool second = frame0 + 1 < p.nframes;           // (a batch with an odd number of frames: the last CTA layer has one)
+    uint8_t* grow = p.dst + (long long)frame0 * p.dstFrameStride + (long long)yb * p.dstPitch + 4 * gq;
+    // one destination row (of both frames) from two filtered source rows: ((c0*(H0>>4))>>16) + ((c1*(H1>>4))>>16) + 2) >> 2.
+    // A multiply-high (IMAD.HI) runs at a quarter of the lane rate on this part, a 32-bit multiply and a dp2a at half of it: the
+    // products (< 2^26) are taken in full and their upper halves summed by dp2a against the byte pair (0, 1), the rounding 2
+    // riding in as the accumulator.  The four sums of a word (<= 1022 each) are shifted and packed two at a time in 16-bit lanes
+    auto emit = [&](const unsigned (&top)[8], const unsigned (&bot)[8], unsigned c0s, unsigned c1s) {
+        const unsigned c0 = c0s >> 12, c1 = c1s >> 12;        // (the table keeps the coefficients shifted for the fused kernel)
         unsigned word[2];
 #pragma unroll
         for (int k = 0; k < 2; k++) {
             unsigned sum[4];
 #pragma unroll
-            for (int i = 0; i < 4; i++) sum[i] = __umulhi(c0, top[4 * k + i]) + __umulhi(c1, bot[4 * k + i]) + 2u;
+            for (int i = 0; i < 4; i++) sum[i] = __dp2a_lo(c1 * bot[4 * k + i], 0x0100u, __dp2a_lo(c0 * top[4 * k + i], 0x0100u, 2u));
             const unsigned ev = sum[0] + (sum[2] << 16), od = sum[1] + (sum[3] << 16);
             word[k] = ((ev >> 2) & 0x00FF00FFu) | ((od << 6) & 0xFF00FF00u);
         }
-        if (ncols == 8) *(uint2*)grow = make_uint2(word[0], word[1]);
-        else {
+        uint8_t* grow1 = grow + p.dstFrameStride;
+        if (ncols == 4) {
+            *(uint32_t*)grow = word[0];
+            if (second) *(uint32_t*)grow1 = word[1];
+        } else {
 #pragma unroll
-            for (int i = 0; i < 8; i++)
-                if (i < ncols) grow[i] = (uint8_t)(word[i >> 2] >> (8 * (i & 3)));
+            for (int i = 0; i < 3; i++)
+                if (i < ncols) {
+                    grow[i] = (uint8_t)(word[0] >> (8 * i));
+                    if (second) grow1[i] = (uint8_t)(word[1] >> (8 * i));
+                }
         }
         grow += p.dstPitch;
     };
@@ -326,14 +338,11 @@ __global__ void __launch_bounds__(32 * PL_WARPS, 7) pyramid_level_kernel(const _
     // (the loop is unrolled by two, so which set holds which row is static and nothing is ever copied); a destination row is
     // emitted at the step that filters its second source row — its first is the row of the step before (the plan checks
     // that the second source rows of a level increase strictly), or the same row where cv::resize clamps at the last row.
-    const int4* ryp = p.ytab + yb;
-    int4 ey = __ldg(ryp), eyNext = __ldg(ryp + 1);       // (the same address in every lane; the table has two spare entries at its end)
-    int srow = ey.x, left = ye - yb;
     unsigned hA[8], hB[8];
     const int srowEnd = srcY0 + p.boxH;                  // (never reached: the band's last row is emitted inside the box; a bound all the same)
 #pragma unroll 1
     while (srow < srowEnd) {
-        hrow(srow, hA);
+        hrow(hA);
         if (srow == ey.y) {
             if (ey.x == ey.y) emit(hA, hA, (unsigned)ey.z, (unsigned)ey.w);
             else emit(hB, hA, (unsigned)ey.z, (unsigned)ey.w);
@@ -341,7 +350,7 @@ __global__ void __launch_bounds__(32 * PL_WARPS, 7) pyramid_level_kernel(const _
             ey = eyNext; ryp++; eyNext = __ldg(ryp + 1);
         }
         srow++;
-        hrow(srow, hB);
+        hrow(hB);
         if (srow == ey.y) {
             if (ey.x == ey.y) emit(hB, hB, (unsigned)ey.z, (unsigned)ey.w);
             else emit(hA, hB, (unsigned)ey.z, (unsigned)ey.w);
@@ -360,6 +369,8 @@ struct PyramidPlan {
     int4* d_yt = nullptr;
     int4* d_xg = nullptr;
     int4* d_qtab = nullptr;
+    int4* d_ptab = nullptr;    // pair taps of the per-level kernel: one int4 per group of four columns
+    bool pairsFit = true;      // the four tap bytes of every pixel pair lie in two consecutive source words
     int4* d_ytab = nullptr;
     bool tapsFit = true;       // every group of four columns finds its eight taps in three consecutive source words
     cudaError_t cudaErr = cudaSuccess;      // first failure of a table allocation / upload
@@ -449,7 +460,7 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         // selLo01 | selHi01 << 16, selLo23 | selHi23 << 16, 0}, int4 #1 = {c0 | c1 << 16 for the four columns}.
         // Tap byte o (0..11, relative to the first word) is routed by two byte-permutes: the first picks from words
         // 0-1, the second substitutes bytes that live in word 2.
-        std::vector<int4> q;
+        std::vector<int4> q, pt;
         for (int l = 1; l < g.nlevels; l++) {
             p.qOff[l] = (int)q.size();
             std::vector<short> s0, s1, c0, c1;
@@ -473,6 +484,19 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
                 }
                 q.push_back(make_int4(wbase, (int)(sel[0][0] | (sel[0][1] << 16)), (int)(sel[1][0] | (sel[1][1] << 16)), 0));
                 q.push_back(make_int4((int)A[0], (int)A[1], (int)A[2], (int)A[3]));
+                // PairTaps (per-level kernel): the four tap bytes of a pixel pair span at most four source bytes, i.e. two
+                // consecutive words: {first word of pair 0-1, first word of pair 2-3, selector 01 | selector 23 << 16, 0} — one
+                // byte-permute per pair instead of two
+                int pw[2]; unsigned ps[2] = { 0, 0 };
+                for (int j = 0; j < 2; j++) {
+                    pw[j] = std::min(std::min(a[4 * j], a[4 * j + 1]), std::min(a[4 * j + 2], a[4 * j + 3])) >> 2;
+                    for (int k = 0; k < 4; k++) {
+                        const int o = a[4 * j + k] - 4 * pw[j];
+                        if (o < 0 || o > 7) { P->pairsFit = false; continue; }
+                        ps[j] |= (unsigned)o << (4 * k);
+                    }
+                }
+                pt.push_back(make_int4(pw[0], pw[1], (int)(ps[0] | (ps[1] << 16)), 0));
             }
         }
         // vertical taps per destination row, coefficients pre-shifted for the multiply-high of the vertical pass
@@ -490,6 +514,8 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         if (q.empty()) q.push_back(make_int4(0, 0, 0, 0));
         upload(P->d_qtab, q);
         p.qtab = P->d_qtab;
+        if (pt.empty()) pt.push_back(make_int4(0, 0, 0, 0));
+        upload(P->d_ptab, pt);
     }
     P->boxW = (mw[0] + 15) & ~15;
     P->boxH = mh[0];
@@ -544,7 +570,7 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         P->lvBoxW[l] = bw; P->lvBoxH[l] = bh;
         if (bw > 256 || bh > 256 || 2 * (size_t)bw * bh + 256 > 200 * 1024) P->lvOk = false;
     }
-    if (!P->tapsFit || !P->encode || P->cudaErr != cudaSuccess) P->lvOk = false;
+    if (!P->tapsFit || !P->pairsFit || !P->encode || P->cudaErr != cudaSuccess) P->lvOk = false;
     return P;
 }
 
@@ -556,7 +582,7 @@ bool os1_pyramid_plan_ok(const PyramidPlan* P)
 void os1_pyramid_plan_destroy(PyramidPlan* P)
 {
     if (!P) return;
-    cudaFree(P->d_xt); cudaFree(P->d_yt); cudaFree(P->d_xg); cudaFree(P->d_qtab); cudaFree(P->d_ytab);
+    cudaFree(P->d_xt); cudaFree(P->d_yt); cudaFree(P->d_xg); cudaFree(P->d_qtab); cudaFree(P->d_ptab); cudaFree(P->d_ytab);
     delete P;
 }
 
@@ -580,7 +606,7 @@ static cudaError_t launch_levels(PyramidPlan* P, const Geometry& g, const DevPtr
         if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
         LvlParams p;
         p.level = l; p.W = D.w; p.H = D.h; p.nframes = nframes; p.boxW = P->lvBoxW[l]; p.boxH = P->lvBoxH[l];
-        p.qtab = P->d_qtab + P->prm.qOff[l]; p.ytab = P->d_ytab + P->prm.yOff[l];
+        p.qtab = P->d_qtab + P->prm.qOff[l]; p.ptab = P->d_ptab + P->prm.qOff[l] / 2; p.ytab = P->d_ytab + P->prm.yOff[l];
         p.dst = d.slab + D.off; p.dstFrameStride = g.slabBytes; p.dstPitch = D.pitch;
         p.dbgSrc = src; p.dbgStride = srcStride; p.dbgPitch = srcPitch; p.dbgW = S.w; p.dbgH = S.h;
         const size_t smem = 2 * (size_t)p.boxW * p.boxH + 128;
