@@ -126,6 +126,29 @@ def ncu_traffic(workload, kernel):
     return None, None
 
 
+def ncu_pipes(workload, kernel):
+    """What the dominant kernel is really held by: busy fractions of the issue slots and of the integer pipes from the same
+    committed `ncu --set full` capture the traffic figure comes from (counters, not a live measurement)."""
+    try:
+        idx = json.load(open(os.path.join(ROOT, "profiles", "index.json")))
+        cap = [c for c in idx["captures"] if c["workload"] == workload][-1]
+        rows = list(csv.reader(open(os.path.join(ROOT, "profiles", cap["raw_csv"]))))
+        head = rows[0]
+        ik = head.index("Kernel Name")
+        names = {"issue_slots_busy_pct": "sm__issue_active.avg.pct_of_peak_sustained_elapsed",
+                 "alu_pipe_busy_pct": "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_elapsed",
+                 "fma_heavy_pipe_busy_pct": "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed",
+                 "dram_busy_pct": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"}
+        for r in rows[2:]:
+            if kernel + "_kernel" in r[ik]:
+                out = {k: float(r[head.index(v)]) for k, v in names.items() if v in head}
+                out["source"] = "profiles/%s" % cap["raw_csv"]
+                return out
+    except Exception:
+        pass
+    return None
+
+
 # ------------------------------------------------------------------------------------------------------------------
 # CPU legs (the only code in this file that touches oracle/)
 def _reference_runner(w, threads):
@@ -456,7 +479,9 @@ class Bench:
                 "algorithmic_bytes_per_launch": dom_bytes, "kernels": per_kernel,
                 "kernel_sum_ms": float(stage_ms.sum()), "kernel_sum_over_step": float(stage_ms.sum() / ms),
                 "whole_step_achieved_gbs": whole, "whole_step_frac": whole / peak,
-                "note": "FAST is bound by the integer ALU pipe and instruction issue, not by HBM: see DESIGN.md section 4"}
+                "pipes": ncu_pipes([k for k, v in WORKLOADS.items() if v is w][0], KERNELS[dom]),
+                "note": "FAST is bound by the integer ALU pipe and instruction issue, not by HBM: see DESIGN.md section 4 "
+                        "(`pipes`: busy fractions from the committed ncu capture)"}
         h2d_bytes = int(B * w["rows"] * w["cols"])
         rec = {"value": world * B / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms,
                "config": {"workload": w["label"], "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,

@@ -30,8 +30,9 @@ struct PyrParams {
     const int4* yt;              // [level][nty]
     const int4* xg;              // [level][ntx]  thread-mapping constants {ngroups, rcp, nbands, rcp}
     const int4* qtab;            // per level, per group of four destination columns: 2 x int4 (see QuadTaps)
+    const int4* ptab;            // per level, per group: 1 x int4 (see PairTaps), first entry of a level = qOff / 2
     int qOff[OS1_MAX_LEVELS];    // first entry (in int4 units) of a level in qtab
-    const int4* ytab;            // per level, per destination row: {source row 0, source row 1, c0 << 12, c1 << 12}
+    const int4* ytab;            // per level, per destination row: {source row 0, source row 1, c0, c1}
     int yOff[OS1_MAX_LEVELS];
     uint8_t* slab;
     long long slabBytes;
@@ -139,26 +140,24 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
             const int rpb = (int)(((unsigned)(rows + nbands - 1) * (unsigned)M.w) >> 24);
             const int yb = band * rpb, ye = min(rows, yb + rpb);
             if (band < nbands && yb < ye) {
-                // horizontal taps of the four columns, prepared on the host (QuadTaps): three consecutive source words
-                // hold all eight taps; two byte-permutes line them up as (p0,p1) byte pairs and one dp2a per pixel does
-                // p0*c0 + p1*c1
+                // horizontal taps of the four columns, prepared on the host: the four tap bytes of a pixel pair lie in two
+                // consecutive source words (PairTaps), one byte-permute lines them up as (p0,p1) byte pairs and one dp2a per
+                // pixel does p0*c0 + p1*c1 (QuadTaps' coefficients)
                 const int gq = (gx0 >> 2) + grp;                 // global group index
-                const int4 t0 = __ldg(p.qtab + p.qOff[l] + 2 * gq), t1 = __ldg(p.qtab + p.qOff[l] + 2 * gq + 1);
-                // first source word, relative to the tile (columns left of the computed range may point before it:
-                // their results are discarded, so any in-bounds word will do)
-                const int wb = max(t0.x - (srcX0 >> 2), 0);
-                const unsigned selLo01 = (unsigned)t0.y & 0xFFFFu, selHi01 = (unsigned)t0.y >> 16;
-                const unsigned selLo23 = (unsigned)t0.z & 0xFFFFu, selHi23 = (unsigned)t0.z >> 16;
+                const int4 t1 = __ldg(p.qtab + p.qOff[l] + 2 * gq + 1), pt = __ldg(p.ptab + (p.qOff[l] >> 1) + gq);
+                // first source words of the two pairs, relative to the tile (columns left of the computed range may point
+                // before it: their results are discarded, so any in-bounds word will do)
+                const int w01 = max(pt.x - (srcX0 >> 2), 0), w23 = max(pt.y - (srcX0 >> 2), 0);
+                const unsigned sel01 = (unsigned)pt.z & 0xFFFFu, sel23 = (unsigned)pt.z >> 16;
                 const unsigned A0 = t1.x, A1 = t1.y, A2 = t1.z, A3 = t1.w;       // c0 | c1 << 16 per column
                 const int gxb = gx0 + 4 * grp;
                 const bool fullX = gxb >= X.z && gxb + 4 <= X.w;
                 const int spw = sp >> 2;
-                const uint32_t* srcw = (const uint32_t*)src + wb - srcY0 * spw;      // word `wb` of global source row 0
+                const uint32_t* srcw = (const uint32_t*)src - srcY0 * spw;           // word 0 of global source row 0
                 auto hrow = [&](int srow, unsigned (&h)[4]) {
                     const uint32_t* r = srcw + srow * spw;
-                    const unsigned w0 = r[0], w1 = r[1], w2 = r[2];
-                    const unsigned B01 = __byte_perm(__byte_perm(w0, w1, selLo01), w2, selHi01);
-                    const unsigned B23 = __byte_perm(__byte_perm(w0, w1, selLo23), w2, selHi23);
+                    const unsigned B01 = __byte_perm(r[w01], r[w01 + 1], sel01);
+                    const unsigned B23 = __byte_perm(r[w23], r[w23 + 1], sel23);
                     // kept as H >> 4, what cv::resize's vertical pass multiplies
                     h[0] = __dp2a_lo(A0, B01, 0u) >> 4;
                     h[1] = __dp2a_hi(A1, B01, 0u) >> 4;
@@ -184,15 +183,13 @@ __global__ void __launch_bounds__(256) pyramid_kernel(const __grid_constant__ CU
                         for (int i = 0; i < 4; i++) h1[i] = h0[i];
                     }
                     prev1 = ey.y;
-                    const unsigned b0 = (unsigned)ey.z >> 12, b1 = (unsigned)ey.w >> 12;
-                    unsigned word = 0;
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        // ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2: full 32-bit products (< 2^26), their upper halves
-                        // summed by dp2a against the byte pair (0, 1) — a multiply-high runs at half the rate of these
-                        const unsigned v = __dp2a_lo(b1 * h1[i], 0x0100u, __dp2a_lo(b0 * h0[i], 0x0100u, 2u)) >> 2;
-                        word |= v << (8 * i);
-                    }
+                    const unsigned b0 = (unsigned)ey.z, b1 = (unsigned)ey.w;
+                    // ((b0*(H0>>4))>>16) + ((b1*(H1>>4))>>16) + 2) >> 2: full 32-bit products (< 2^26; a multiply-high runs at half
+                    // the rate of a multiply here), their upper halves picked out two pixels at a time by a byte-permute, one
+                    // add per two pixels in 16-bit lanes (sums <= 1022: no carry between the lanes), rounding included
+                    const unsigned ev = __byte_perm(b0 * h0[0], b0 * h0[2], 0x7632) + __byte_perm(b1 * h1[0], b1 * h1[2], 0x7632) + 0x00020002u;
+                    const unsigned od = __byte_perm(b0 * h0[1], b0 * h0[3], 0x7632) + __byte_perm(b1 * h1[1], b1 * h1[3], 0x7632) + 0x00020002u;
+                    const unsigned word = ((ev >> 2) & 0x00FF00FFu) | ((od << 6) & 0xFF00FF00u);
                     *dp = word;
                     if (ly >= o0 && ly < o1) {
                         if (fullX) *(uint32_t*)grow = word;
@@ -306,18 +303,19 @@ __global__ void __launch_bounds__(32 * PL_WARPS, 7) pyramid_level_kernel(const _
     const bool second = frame0 + 1 < p.nframes;           // (a batch with an odd number of frames: the last CTA layer has one)
     uint8_t* grow = p.dst + (long long)frame0 * p.dstFrameStride + (long long)yb * p.dstPitch + 4 * gq;
     // one destination row (of both frames) from two filtered source rows: ((c0*(H0>>4))>>16) + ((c1*(H1>>4))>>16) + 2) >> 2.
-    // A multiply-high (IMAD.HI) runs at a quarter of the lane rate on this part, a 32-bit multiply and a dp2a at half of it: the
-    // products (< 2^26) are taken in full and their upper halves summed by dp2a against the byte pair (0, 1), the rounding 2
-    // riding in as the accumulator.  The four sums of a word (<= 1022 each) are shifted and packed two at a time in 16-bit lanes
-    auto emit = [&](const unsigned (&top)[8], const unsigned (&bot)[8], unsigned c0s, unsigned c1s) {
-        const unsigned c0 = c0s >> 12, c1 = c1s >> 12;        // (the table keeps the coefficients shifted for the fused kernel)
+    // A multiply-high (IMAD.HI) runs at a quarter of the lane rate on this part, a 32-bit multiply at half of it: the products
+    // (< 2^26) are taken in full and their upper halves, which are what is wanted, picked out two pixels at a time by a
+    // byte-permute.  The four sums of a word are then shifted and merged in their 16-bit lanes
+    auto emit = [&](const unsigned (&top)[8], const unsigned (&bot)[8], unsigned c0, unsigned c1) {
         unsigned word[2];
 #pragma unroll
         for (int k = 0; k < 2; k++) {
-            unsigned sum[4];
-#pragma unroll
-            for (int i = 0; i < 4; i++) sum[i] = __dp2a_lo(c1 * bot[4 * k + i], 0x0100u, __dp2a_lo(c0 * top[4 * k + i], 0x0100u, 2u));
-            const unsigned ev = sum[0] + (sum[2] << 16), od = sum[1] + (sum[3] << 16);
+            const unsigned* t = top + 4 * k;
+            const unsigned* b = bot + 4 * k;
+            // upper halves of the products of pixels (0, 2) and of pixels (1, 3) side by side in 16-bit lanes: one add per
+            // two pixels gives their sums (<= 1022: no carry between the lanes), rounding included
+            const unsigned ev = __byte_perm(c0 * t[0], c0 * t[2], 0x7632) + __byte_perm(c1 * b[0], c1 * b[2], 0x7632) + 0x00020002u;
+            const unsigned od = __byte_perm(c0 * t[1], c0 * t[3], 0x7632) + __byte_perm(c1 * b[1], c1 * b[3], 0x7632) + 0x00020002u;
             word[k] = ((ev >> 2) & 0x00FF00FFu) | ((od << 6) & 0xFF00FF00u);
         }
         uint8_t* grow1 = grow + p.dstFrameStride;
@@ -499,13 +497,13 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
                 pt.push_back(make_int4(pw[0], pw[1], (int)(ps[0] | (ps[1] << 16)), 0));
             }
         }
-        // vertical taps per destination row, coefficients pre-shifted for the multiply-high of the vertical pass
+        // vertical taps per destination row
         std::vector<int4> yt4;
         for (int l = 1; l < g.nlevels; l++) {
             p.yOff[l] = (int)yt4.size();
             std::vector<short> s0, s1, c0, c1;
             os1_host_resize_taps(g.lv[l - 1].h, g.lv[l].h, true, s0, s1, c0, c1);
-            for (int y = 0; y < g.lv[l].h; y++) yt4.push_back(make_int4(s0[y], s1[y], (int)c0[y] << 12, (int)c1[y] << 12));
+            for (int y = 0; y < g.lv[l].h; y++) yt4.push_back(make_int4(s0[y], s1[y], (int)c0[y], (int)c1[y]));
         }
         yt4.push_back(make_int4(0, 0, 0, 0));           // spare entries: pyramid_level_kernel reads two rows ahead
         yt4.push_back(make_int4(0, 0, 0, 0));
@@ -516,6 +514,7 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
         p.qtab = P->d_qtab;
         if (pt.empty()) pt.push_back(make_int4(0, 0, 0, 0));
         upload(P->d_ptab, pt);
+        p.ptab = P->d_ptab;
     }
     P->boxW = (mw[0] + 15) & ~15;
     P->boxH = mh[0];
@@ -576,7 +575,7 @@ PyramidPlan* os1_pyramid_plan_create(const Geometry& g, int tileW, int tileH)
 
 bool os1_pyramid_plan_ok(const PyramidPlan* P)
 {
-    return P && P->cudaErr == cudaSuccess && P->encode && P->tapsFit && P->boxW <= 256 && P->boxH <= 256 && P->smemBytes <= 200 * 1024;
+    return P && P->cudaErr == cudaSuccess && P->encode && P->tapsFit && P->pairsFit && P->boxW <= 256 && P->boxH <= 256 && P->smemBytes <= 200 * 1024;
 }
 
 void os1_pyramid_plan_destroy(PyramidPlan* P)
