@@ -238,3 +238,38 @@ def test_per_level_pyramid_launches_for_batches(oracle_lib, shape, nf, sf, nl, s
     for f in range(B):
         assert np.array_equal(dh[f, :ch[f]], dd[f, :ch[f]]), "frame %d" % f
     e.close()
+
+
+@pytest.mark.parametrize("shape,nf", [((1080, 1920), 2000), ((720, 1280), 1500), ((481, 643), 1000)])
+def test_per_level_and_fused_pyramids_agree_at_full_size(oracle_lib, shape, nf):
+    """BASELINE sizes, 64 frames on the device: the per-level launches (whole batch) and the fused chain (the same frames in
+    batches of 16) are two independent kernels — every keypoint and descriptor byte of every frame must agree, and the pyramid bytes
+    of a frame equal the oracle's."""
+    import torch
+    B = 64
+    frames = synth.video(B, shape[0], shape[1], seed=90)
+    e = gpu_ext(nf, 1.2, 8, 20, 7)
+    cap = e.max_keypoints()
+    fd = torch.from_numpy(frames).cuda()
+    out = []
+    for step in (B, 16):
+        kp = torch.zeros((B, cap, 28), dtype=torch.uint8, device="cuda"); desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda")
+        cnt = torch.zeros(B, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        for f0 in range(0, B, step):
+            e.extract_batch_raw(fd[f0:].data_ptr(), step, shape[0], shape[1], shape[1], shape[0] * shape[1], True,
+                                kp[f0:].data_ptr(), desc[f0:].data_ptr(), cap, cnt[f0:].data_ptr(), True)
+            e.synchronize()
+            assert e.launches_per_call() == (10 if step == B else 4)
+        if step == B:
+            o = oracle_lib.Oracle(nf, 1.2, 8, 20, 7)
+            o.extract(frames[B - 1])
+            for l in range(8):
+                assert np.array_equal(o.level_pixels(l), e.pyramid_level(l, B - 1)), "pyramid level %d" % l
+        out.append((kp.cpu().numpy(), desc.cpu().numpy(), cnt.cpu().numpy()))
+    (k0, d0, c0), (k1, d1, c1) = out
+    assert np.array_equal(c0, c1) and c0.min() > 0
+    for f in range(B):
+        n = int(c0[f])
+        assert np.array_equal(k0[f, :n], k1[f, :n]) and np.array_equal(d0[f, :n], d1[f, :n]), "frame %d" % f
+    e.close()
