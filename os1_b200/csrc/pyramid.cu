@@ -622,23 +622,27 @@ static cudaError_t launch_levels(PyramidPlan* P, const Geometry& g, const DevPtr
 
 bool os1_pyramid_plan_levels_ok(const PyramidPlan* P) { return P && P->lvOk; }
 
-// frames from which a batch takes the per-level launches (below, the fused chain's single launch wins: measured cross-over)
-static int levels_min_frames()
+// Frames from which a batch takes the per-level launches.  Seven launches cost about 60 us whatever the batch (launch latency,
+// the tail of each small grid), the fused chain's single launch nothing: measured cross-over at about 32 M pixels per call (16 frames
+// of 1920x1080, 35 of 1280x720, 100 of 640x480; scripts/pyr_crossover.py).  OS1_PYR_LEVELS_MIN=<frames> overrides (tests, experiments).
+static int levels_min_frames(const Geometry& g)
 {
-    static const int lvMin = getenv("OS1_PYR_LEVELS_MIN") ? atoi(getenv("OS1_PYR_LEVELS_MIN")) : 64;
-    return lvMin;
+    const char* env = getenv("OS1_PYR_LEVELS_MIN");          // (read at every call: the tests switch paths inside one process)
+    const int envMin = env ? atoi(env) : 0;
+    if (envMin > 0) return envMin;
+    return (int)((32000000LL + (long long)g.rows * g.cols - 1) / ((long long)g.rows * g.cols));
 }
 
 int os1_pyramid_launch_count(const PyramidPlan* P, const Geometry& g, int nframes)
 {
     if (g.nlevels < 2) return 0;
-    return (P && P->lvOk && nframes >= levels_min_frames()) ? g.nlevels - 1 : 1;
+    return (P && P->lvOk && nframes >= levels_min_frames(g)) ? g.nlevels - 1 : 1;
 }
 
 cudaError_t os1_launch_pyramid(PyramidPlan* P, const Geometry& g, const DevPtrs& d, int nframes, cudaStream_t s)
 {
     if (g.nlevels < 2) return cudaSuccess;
-    if (P && P->lvOk && nframes >= levels_min_frames()) return launch_levels(P, g, d, nframes, s);
+    if (P && P->lvOk && nframes >= levels_min_frames(g)) return launch_levels(P, g, d, nframes, s);
     if (!os1_pyramid_plan_ok(P)) return cudaErrorNotSupported;
     CUtensorMap tmap;
     cuuint64_t dims[3] = { (cuuint64_t)g.cols, (cuuint64_t)g.rows, (cuuint64_t)nframes };

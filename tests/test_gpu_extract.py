@@ -198,12 +198,13 @@ def test_full_size_properties_1080p_batch():
 
 @pytest.mark.parametrize("shape,nf,sf,nl,seed", [((240, 320), 500, 1.2, 8, 70), ((333, 517), 700, 1.2, 8, 71), ((300, 420), 400, 1.5, 5, 72),
                                                  ((131, 257), 300, 1.2, 6, 73)])
-def test_per_level_pyramid_launches_for_batches(oracle_lib, shape, nf, sf, nl, seed):
-    """Batches of 64 frames or more build the pyramid with one launch per level (csrc/pyramid.cu: pyramid_level_kernel) instead of
+def test_per_level_pyramid_launches_for_batches(oracle_lib, monkeypatch, shape, nf, sf, nl, seed):
+    """Large batches (from about 32 M pixels per call; here from 64 frames) build the pyramid with one launch per level (csrc/pyramid.cu: pyramid_level_kernel) instead of
     the fused chain: same bytes at every level (tiles cut by the image edge, images narrower than a tile, a tile row of one
     pixel row), and the same keypoints and descriptors as the frames extracted one by one."""
     import torch
     from os1_b200 import KEYPOINT_DTYPE
+    monkeypatch.setenv("OS1_PYR_LEVELS_MIN", "64")          # (by default the switch is at about 32 M pixels per call)
     B = 66
     frames = synth.video(B, shape[0], shape[1], seed=seed)
     e = gpu_ext(nf, sf, nl, 20, 7)
@@ -241,11 +242,12 @@ def test_per_level_pyramid_launches_for_batches(oracle_lib, shape, nf, sf, nl, s
 
 
 @pytest.mark.parametrize("shape,nf", [((1080, 1920), 2000), ((720, 1280), 1500), ((481, 643), 1000)])
-def test_per_level_and_fused_pyramids_agree_at_full_size(oracle_lib, shape, nf):
+def test_per_level_and_fused_pyramids_agree_at_full_size(oracle_lib, monkeypatch, shape, nf):
     """BASELINE sizes, 64 frames on the device: the per-level launches (whole batch) and the fused chain (the same frames in
     batches of 16) are two independent kernels — every keypoint and descriptor byte of every frame must agree, and the pyramid bytes
     of a frame equal the oracle's."""
     import torch
+    monkeypatch.setenv("OS1_PYR_LEVELS_MIN", "64")
     B = 64
     frames = synth.video(B, shape[0], shape[1], seed=90)
     e = gpu_ext(nf, 1.2, 8, 20, 7)
@@ -272,4 +274,25 @@ def test_per_level_and_fused_pyramids_agree_at_full_size(oracle_lib, shape, nf):
     for f in range(B):
         n = int(c0[f])
         assert np.array_equal(k0[f, :n], k1[f, :n]) and np.array_equal(d0[f, :n], d1[f, :n]), "frame %d" % f
+    e.close()
+
+
+def test_pyramid_path_switch_by_pixels_per_call():
+    """Without the override the per-level launches start at about 32 M pixels per call: 16 frames of 1920x1080."""
+    import torch
+    assert "OS1_PYR_LEVELS_MIN" not in os.environ
+    frames = torch.from_numpy(synth.video(16, 1080, 1920, seed=91)).cuda()
+    e = gpu_ext(2000, 1.2, 8, 20, 7)
+    cap = e.max_keypoints()
+    kp = torch.zeros((16, cap, 28), dtype=torch.uint8, device="cuda"); desc = torch.zeros((16, cap, 32), dtype=torch.uint8, device="cuda")
+    cnt = torch.zeros(16, dtype=torch.int32, device="cuda")
+    res = []
+    for n, launches in ((16, 10), (15, 4)):
+        e.extract_batch_raw(frames.data_ptr(), n, 1080, 1920, 1920, 1080 * 1920, True, kp.data_ptr(), desc.data_ptr(), cap, cnt.data_ptr(), True)
+        e.synchronize()
+        assert e.launches_per_call() == launches
+        res.append((cnt[:15].cpu().numpy().copy(), desc[:15].cpu().numpy().copy()))
+    assert np.array_equal(res[0][0], res[1][0])
+    for f in range(15):
+        assert np.array_equal(res[0][1][f, :res[0][0][f]], res[1][1][f, :res[0][0][f]])
     e.close()
