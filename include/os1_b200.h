@@ -87,7 +87,8 @@ int os1_orb_extract_batch(os1_orb* h, const uint8_t* frames, int nframes, int ro
 int os1_orb_synchronize(os1_orb* h);
 /* Make the handle enqueue on a caller-owned cudaStream_t (NULL restores the handle's own stream). */
 int os1_orb_set_stream(os1_orb* h, void* cuda_stream);
-/* Number of kernels one extract call launches (for launch accounting). */
+/* Number of kernels the handle's last extract call launched (for launch accounting): 4 — pyramid, FAST, quadtree, describe — per
+ * chunk, or nlevels - 1 + 3 where a large device-resident batch builds its pyramid with one launch per level. */
 int os1_orb_launches_per_call(const os1_orb* h);
 /* Measurement aid (no reference counterpart): with timing enabled every extract call brackets its four kernels
  * (pyramid, FAST, quadtree, describe) with CUDA events on the handle's stream; os1_orb_get_stage_times waits for
