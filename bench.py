@@ -364,7 +364,8 @@ class Bench:
             self.step_device()
         e1.record(self.xstream)
         self.barrier()
-        ms = self.reduce_max(e0.elapsed_time(e1))
+        ms_local = e0.elapsed_time(e1)
+        ms = self.reduce_max(ms_local)
         self.ext.synchronize()                                              # (reads the device-side status word: capacity errors surface here)
         clocks = None
         if sampler is not None:
@@ -373,7 +374,16 @@ class Bench:
                 src = "under load immediately before the timed region (it was shorter than the 50 ms sampling period)"
             else:
                 src = "during the timed region"
+            pw = [float(r[2]) for r in sampler.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
             clocks = sampler.finish(); clocks["sampled"] = src
+            if self.dist is not None:
+                # the step is the slowest rank's: every rank's own time, clock and power, so that a slow GPU shows as such
+                mine = torch.tensor([ms_local / steps, clocks["sm_mhz"] or 0.0, float(np.median(pw)) if pw else 0.0], device=self.dev, dtype=torch.float64)
+                allr = torch.empty((self.dist.get_world_size(), 3), device=self.dev, dtype=torch.float64)
+                self.dist.all_gather_into_tensor(allr.view(-1), mine)
+                a = allr.cpu().numpy()
+                clocks["per_rank"] = {"ms_per_step": [round(float(v), 4) for v in a[:, 0]], "sm_mhz": [float(v) for v in a[:, 1]],
+                                      "power_w": [round(float(v), 1) for v in a[:, 2]]}
         return ms / steps, clocks
 
     def measure_stages(self, reps=5):
