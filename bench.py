@@ -306,7 +306,9 @@ class Bench:
         from os1_b200 import synth
         self.torch, self.w, self.B, self.dev, self.dist = torch, w, B, dev, dist
         R, Cc = w["rows"], w["cols"]
-        self.frames_h = torch.from_numpy(synth.video(B, R, Cc, seed=1000 + rank)).pin_memory()
+        # every rank runs the SAME seeded stream: weak scaling means the same work per GPU, and FAST's cost follows the content
+        # (with a stream per rank the step times of the ranks differ by up to 10 %; the step is the slowest rank's)
+        self.frames_h = torch.from_numpy(synth.video(B, R, Cc, seed=1000)).pin_memory()
         self.frames_d = self.frames_h.to(dev, non_blocking=False)          # resident in HBM before any timed region
         self.ext = os1_b200.ORBextractor(*params(w), device=dev.index)
         self.cap = self.ext.max_keypoints()
@@ -496,7 +498,7 @@ class Bench:
         rec = {"value": world * B / (ms * 1e-3), "unit": "frames/s", "ms_per_step": ms,
                "config": {"workload": w["label"], "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,
                           "l2": "inputs larger than L2 (%d MB of frames per step per GPU, plus the pyramid)" % (h2d_bytes >> 20),
-                          "parallelism": "frame-sharded, %d rank(s), no data-path collective" % world},
+                          "parallelism": "frame-sharded, %d rank(s), no data-path collective; every rank runs the same seeded stream" % world},
                "e2e": {"value": world * B / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d_bytes,
                        "d2h_bytes_per_step": int(B * self.cap * 60 + B * 4 + 4), "ms_per_step": e2e_ms},
                "roofline": roof, "launches_per_step": launches_per_step}
@@ -689,6 +691,9 @@ def sweep_config5(torch, dist, hb, rank, world, local_rank):
     from os1_b200 import shard
     dev = hb.dev
     Fl = min(SWEEP_FRAMES_PER_RANK, hb.B)
+    # the sweep is over DISTINCT frames: every rank gets its own seeded stream here (the headline measurement is over)
+    from os1_b200 import synth
+    hb.frames_d[:Fl].copy_(torch.from_numpy(synth.video(Fl, hb.w["rows"], hb.w["cols"], seed=2000 + rank)))
     stream = torch.cuda.current_stream(dev)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     hb.step_device(Fl); hb.ext.synchronize()
